@@ -1,0 +1,142 @@
+/*
+ * mp_b200.h -- C ABI of the B200-native matrix-profile engine (libmpb200.so).
+ *
+ * This is the drop-in boundary for the hot path of jlscheerer/matrix-profile-hls: it replaces the
+ * OpenCL/XRT wrapper include/host/OpenCL.hpp and the FPGA kernel behind it.  Plain pointers and
+ * sizes only; no exceptions cross it; every function returns MPB_OK (0) or a negative MPB_E_* code
+ * and mpb_last_error() describes the failure.  Citations are file:line relative to the reference.
+ *
+ * There is NO CPU fallback: every compute entry point fails with MPB_E_NO_DEVICE when no CUDA
+ * device is usable.
+ *
+ * Record layouts are byte-identical to include/Config.hpp.in:43-73:
+ *   aggregate_t    { data_t value; int32 index; }            16 B (double, 4 B padding) / 8 B (float)
+ *   InputDataPack  { data_t QT, df, dg, inv; }               32 B / 16 B
+ *   OutputDataPack { aggregate_t rowAggregate, columnAggregate; }   32 B / 16 B
+ */
+#ifndef MP_B200_H
+#define MP_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPB_OK 0
+#define MPB_E_INVALID (-1)    /* bad argument (the reference's ConfigurationError, OpenCL.hpp:48-52) */
+#define MPB_E_NO_DEVICE (-2)  /* no usable CUDA device: there is no CPU fallback */
+#define MPB_E_CUDA (-3)       /* CUDA runtime failure (the reference's RuntimeError, OpenCL.hpp:54-60) */
+#define MPB_E_NOMEM (-4)
+
+/* MP_DATA_TYPE (CMakeLists.txt:35-37) */
+#define MPB_F64 0
+#define MPB_F32 1
+
+/* mpb_plan flags */
+#define MPB_FLAG_STRICT 1u  /* un-fused QT update (mul,mul,add,add): bit-identical to the reference chain, 6 instead of 4 FP64 ops per cell */
+
+typedef struct mpb_context mpb_context; /* replaces OpenCL::Context   (OpenCL.hpp:73-107, 294-317) */
+typedef struct mpb_buffer mpb_buffer;   /* replaces OpenCL::Buffer<T> (OpenCL.hpp:109-211) */
+typedef struct mpb_plan mpb_plan;       /* whole-problem engine state (no reference equivalent: the
+                                           reference sizes everything at configure time) */
+
+const char *mpb_last_error(void);
+const char *mpb_version(void);
+
+/* ---- device runtime: what host/MatrixProfileHost.cpp:69-97,110-122 uses of OpenCL.hpp ---- */
+int mpb_device_count(int *count);
+/* OpenCL::Context() (OpenCL.hpp:294-298): opens device `ordinal`, creates its command stream. */
+int mpb_context_create(int ordinal, mpb_context **ctx);
+int mpb_context_destroy(mpb_context *ctx);
+/* Context::Finish() (OpenCL.hpp:85-89): waits for all enqueued work; *elapsed_ns (may be NULL) gets the
+ * device time spent since the previous Finish (CUDA events), as the reference returns nanoseconds. */
+int mpb_context_finish(mpb_context *ctx, int64_t *elapsed_ns);
+/* The CUDA stream (cudaStream_t) work is enqueued on, for callers that time with their own events. */
+void *mpb_context_stream(mpb_context *ctx);
+int mpb_context_device(mpb_context *ctx);
+/* Context::MakeBuffer<T,Access>(bank, count) (OpenCL.hpp:305-308; ctor :113-127). No memory banks on a GPU. */
+int mpb_buffer_create(mpb_context *ctx, size_t bytes, mpb_buffer **buf);
+int mpb_buffer_destroy(mpb_buffer *buf);
+/* Buffer::CopyFromHost(begin,end) (OpenCL.hpp:131-141): asynchronous enqueue; completes by Finish(). */
+int mpb_buffer_copy_from_host(mpb_buffer *buf, const void *src, size_t bytes);
+/* Buffer::CopyToHost(ptr,count) (OpenCL.hpp:155-161): blocking read. */
+int mpb_buffer_copy_to_host(mpb_buffer *buf, void *dst, size_t bytes);
+void *mpb_buffer_device_ptr(mpb_buffer *buf);
+size_t mpb_buffer_size(mpb_buffer *buf);
+
+/* ---- kernel-level contract: MatrixProfileKernelTLF(n, m, iteration, input, output)
+ *      (kernel/MatrixProfileKernelVanilla.cpp:16-17, kernel/MatrixProfileKernelTiled.cpp:250-251;
+ *      plugin interface test/include/MatrixProfileTests.hpp:67).  w (MP_SIZE_W) and data_t are
+ *      configure-time constants upstream and explicit arguments here.
+ * Computes diagonal chunk `iteration` ([iteration*w, (iteration+1)*w)) over rows [0, n-m+1-iteration*w):
+ * output[i] = { row aggregate of row i, column aggregate of column iteration*w + i }, including the
+ * kernels' P=0 substitution for excluded / out-of-range cells and the Vanilla kernel's tie order, with
+ * un-fused arithmetic -- byte-for-byte what the reference kernel compiled as plain C++ writes
+ * (field bytes; struct padding is zeroed).
+ * Kernel::SetKernelArguments(0, n, m, iteration, bufIn, bufOut) + Kernel::EnqueueTask()
+ * (OpenCL.hpp:246-267, 379-381; call sites host/MatrixProfileHost.cpp:110-113). Asynchronous. */
+int mpb_kernel_tlf_enqueue(mpb_context *ctx, int dtype, int n, int m, int w, int iteration,
+                           const mpb_buffer *input, mpb_buffer *output);
+/* Host-pointer form of the same contract (what a MatrixProfileKernel<data_t,int,w> subclass calls):
+ * copies input (n-m+1 InputDataPacks) to the device, runs the chunk, copies back nRows OutputDataPacks. */
+int mpb_kernel_tlf_f64(int n, int m, int w, int iteration, const void *input, void *output);
+int mpb_kernel_tlf_f32(int n, int m, int w, int iteration, const void *input, void *output);
+
+/* ---- whole-problem engine: the device section of RunMatrixProfileKernel
+ *      (host/MatrixProfileHost.cpp:66-142) in three kernels: precompute (PreComputeStatistics,
+ *      include/host/HostSideComputation.hpp:20-45), SCAMP diagonal bands (both kernels + the
+ *      UpdateAggregates merge, :72-90, fused), finalize (PostComputeAggregates, :47-69). ---- */
+typedef struct {
+    double h2d_ms, precompute_ms, compute_ms, finalize_ms, d2h_ms, total_ms; /* device times (CUDA events) */
+    int64_t cells;        /* useful cells L(L+1)/2, L = n-m+1 - m/4 */
+    int64_t slow_updates; /* profile updates that went through the exact 128-bit CAS path */
+    int32_t launches;     /* kernels launched by the last run */
+    int32_t bands;        /* diagonal bands this rank walked */
+} mpb_timings;
+
+/* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised
+ * Euclidean distance) and MPI[n-m+1] int32 out -- the .tsb -> .mpb/.mpib contract
+ * (include/host/FileIO.hpp:24-48,105-121; host/MatrixProfileHost.cpp:62,144-153). */
+int mpb_compute(mpb_context *ctx, const double *T, int n, int m, int dtype, unsigned flags,
+                double *MP, int32_t *MPI, mpb_timings *timings);
+
+/* Plan form: buffers stay resident in HBM between steps. */
+int mpb_plan_create(mpb_context *ctx, int n, int m, int dtype, unsigned flags, mpb_plan **plan);
+int mpb_plan_destroy(mpb_plan *plan);
+/* Diagonal-band shard: this plan walks bands b with b % world == rank (the reference's round-robin of
+ * chunks over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:101-128). Default (0, 1). */
+int mpb_plan_set_shard(mpb_plan *plan, int rank, int world);
+int mpb_plan_upload_series(mpb_plan *plan, const double *T_host);   /* async H2D of T[n] */
+void *mpb_plan_series_device_ptr(mpb_plan *plan);                   /* double[n] in HBM, caller may fill it */
+int mpb_plan_precompute(mpb_plan *plan);                            /* kernel (1) */
+int mpb_plan_compute(mpb_plan *plan);                               /* kernel (2) over this rank's bands */
+/* Split the packed (corr, index) profile into two dense device arrays for an external max-reduction
+ * (NCCL through torch.distributed): corr_out float64[n-m+1] (non-negative, so its int64 bit pattern is
+ * order-preserving), index_out int32[n-m+1]. */
+int mpb_plan_export(mpb_plan *plan, void *corr_out_dev, void *index_out_dev);
+/* After corr was max-reduced across ranks: index_dev[i] = (my corr == corr_max_dev[i]) ? my index : INT32_MAX,
+ * so that a min-reduction of index_dev picks the smallest index among the ranks holding the maximum. */
+int mpb_plan_mask_index(mpb_plan *plan, const void *corr_max_dev, void *index_dev);
+int mpb_plan_import(mpb_plan *plan, const void *corr_dev, const void *index_dev);
+/* In-library merge over NVLink peer memory (single process, several devices): folds the profiles of
+ * `others` into `plan` with an exact (corr, index) max; peers are read through P2P loads. */
+int mpb_plan_merge_peers(mpb_plan *plan, mpb_plan *const *others, int count);
+int mpb_plan_finalize(mpb_plan *plan);                              /* kernel (3): Pearson -> distance */
+int mpb_plan_download(mpb_plan *plan, double *MP_host, int32_t *MPI_host, double *corr_host /* may be NULL */);
+void *mpb_plan_mp_device_ptr(mpb_plan *plan);                       /* double[n-m+1] */
+void *mpb_plan_mpi_device_ptr(mpb_plan *plan);                      /* int32[n-m+1] */
+/* The precomputed InputDataPack[n-m+1] (reference layout), for parity checks of kernel (1). */
+int mpb_plan_download_input(mpb_plan *plan, void *input_host);
+int mpb_plan_timings(mpb_plan *plan, mpb_timings *out);
+int64_t mpb_useful_cells(int n, int m);
+
+/* ---- measurement support ---- */
+/* Register-resident DFMA (dtype MPB_F64) / FFMA (MPB_F32) issue-rate microbenchmark on ctx's device:
+ * *fma_per_s = fused multiply-adds retired per second over `iters` dependent-chain iterations per thread.
+ * This is the denominator of the FMA roofline. */
+int mpb_measure_fma_peak(mpb_context *ctx, int dtype, int iters, double *fma_per_s, double *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,43 @@
+// mp_kernels.h -- host-side launchers of the engine's kernels (internal to libmpb200.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mpb {
+struct ProfileEntry;
+
+// kernel (1): precompute.cu
+cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream_t s);
+cudaError_t launch_stats_f64(const double *T, const double *mu, int n, int m, double *df_dg, double *inv, double *qt0, cudaStream_t s);
+cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, float *df_dg, float *inv, float *qt0, cudaStream_t s);
+cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s);
+cudaError_t launch_pack_input_f64(const double *df_dg, const double *inv, const double *qt0, int sublen, void *out, cudaStream_t s);
+cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const float *qt0, int sublen, void *out, cudaStream_t s);
+
+// kernel (2): scamp_diag.cu -- diagonal bands [excl + b*BAND_W, ...) for b = rank, rank+world, ...
+struct BandLaunch {
+    int sublen, excl, rank, world;
+    bool strict;
+    unsigned long long *slow_counter;   // device counter of exact-path updates (may be null)
+};
+int band_count(int sublen, int excl);                    // total number of bands of the problem
+cudaError_t launch_bands_f64(const double *df_dg, const double *inv, const double *qt0, ProfileEntry *prof,
+                             const BandLaunch &p, int *launched_ctas, cudaStream_t s);
+cudaError_t launch_bands_f32(const float *df_dg, const float *inv, const float *qt0, ProfileEntry *prof,
+                             const BandLaunch &p, int *launched_ctas, cudaStream_t s);
+
+// kernel (3): merge.cu
+cudaError_t launch_finalize(const ProfileEntry *prof, int sublen, int m, double *MP, int32_t *MPI, double *corr, cudaStream_t s);
+cudaError_t launch_export(const ProfileEntry *prof, int sublen, double *corr, int32_t *index, cudaStream_t s);
+cudaError_t launch_mask_index(const ProfileEntry *prof, int sublen, const double *corr_max, int32_t *index, cudaStream_t s);
+cudaError_t launch_import(ProfileEntry *prof, int sublen, const double *corr, const int32_t *index, cudaStream_t s);
+cudaError_t launch_merge_peer(ProfileEntry *prof, const ProfileEntry *peer, int sublen, cudaStream_t s);
+
+// chunk-compatible MatrixProfileKernelTLF: chunk_tlf.cu
+cudaError_t launch_chunk_tlf_f64(int n, int m, int w, int iteration, const void *input, void *output, void *scratch, size_t scratch_bytes, cudaStream_t s);
+cudaError_t launch_chunk_tlf_f32(int n, int m, int w, int iteration, const void *input, void *output, void *scratch, size_t scratch_bytes, cudaStream_t s);
+size_t chunk_tlf_scratch_bytes(int n, int m);
+
+// measurement: peak_fma.cu
+cudaError_t launch_fma_peak(int dtype, int iters, int blocks, double *sink, cudaStream_t s);
+}  // namespace mpb

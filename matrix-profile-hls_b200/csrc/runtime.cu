@@ -1,0 +1,488 @@
+// runtime.cu -- implementation of the C ABI in include/mp_b200.h over the CUDA runtime.
+// Replaces the reference's OpenCL/XRT wrapper include/host/OpenCL.hpp (Context / Buffer / Program /
+// Kernel) and hosts the whole-problem engine (plan) that drives kernels (1)-(3).
+#include "../../include/mp_b200.h"
+#include "mp_common.cuh"
+#include "mp_kernels.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace mpb {
+int fma_peak_chains();
+int fma_peak_threads();
+}
+
+namespace {
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(expr)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (expr);                                                                    \
+        if (e__ != cudaSuccess)                                                                      \
+            return fail(e__ == cudaErrorMemoryAllocation ? MPB_E_NOMEM : MPB_E_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+}  // namespace
+
+struct mpb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t mark = nullptr, now = nullptr;   // Finish() reports device time since the last Finish()
+    void *tlf_scratch = nullptr;
+    size_t tlf_scratch_bytes = 0;
+    int sm_count = 0;
+};
+
+struct mpb_buffer {
+    mpb_context *ctx = nullptr;
+    void *ptr = nullptr;
+    size_t bytes = 0;
+};
+
+struct mpb_plan {
+    mpb_context *ctx = nullptr;
+    int n = 0, m = 0, sublen = 0, excl = 0, np = 0, dtype = MPB_F64;
+    unsigned flags = 0;
+    int rank = 0, world = 1;
+    double *T = nullptr, *mu = nullptr;
+    void *df_dg = nullptr, *inv = nullptr, *qt0 = nullptr;    // data_t arrays, zero-padded to np
+    mpb::ProfileEntry *prof = nullptr;                        // np slots
+    double *MP = nullptr, *corr = nullptr;
+    int32_t *MPI = nullptr;
+    unsigned long long *slow_counter = nullptr;
+    cudaEvent_t ev[8] = {};
+    mpb_timings tm = {};
+    bool ran_h2d = false;
+};
+
+extern "C" {
+
+const char *mpb_last_error(void) { return g_err; }
+const char *mpb_version(void) { return "mpb200 0.1 (sm_100a; DPT=8, BAND_W=1024, TILE_H=256)"; }
+
+int mpb_device_count(int *count) {
+    if (!count) return fail(MPB_E_INVALID, "count is null");
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess || c == 0) {
+        *count = 0;
+        cudaGetLastError();
+        return fail(MPB_E_NO_DEVICE, "no CUDA device: %s", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+    }
+    *count = c;
+    return MPB_OK;
+}
+
+int mpb_context_create(int ordinal, mpb_context **out) {
+    if (!out) return fail(MPB_E_INVALID, "ctx out-pointer is null");
+    *out = nullptr;
+    int count = 0;
+    int rc = mpb_device_count(&count);
+    if (rc != MPB_OK) return rc;
+    if (ordinal < 0 || ordinal >= count) return fail(MPB_E_INVALID, "device ordinal %d out of range [0,%d)", ordinal, count);
+    CU(cudaSetDevice(ordinal));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, ordinal));
+    if (prop.major < 10) return fail(MPB_E_NO_DEVICE, "device %d is sm_%d%d; this library carries sm_100a code only", ordinal, prop.major, prop.minor);
+    mpb_context *c = new (std::nothrow) mpb_context();
+    if (!c) return fail(MPB_E_NOMEM, "out of host memory");
+    c->device = ordinal;
+    c->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->mark));
+    CU(cudaEventCreate(&c->now));
+    CU(cudaEventRecord(c->mark, c->stream));
+    *out = c;
+    return MPB_OK;
+}
+
+int mpb_context_destroy(mpb_context *c) {
+    if (!c) return MPB_OK;
+    cudaSetDevice(c->device);
+    if (c->tlf_scratch) cudaFree(c->tlf_scratch);
+    if (c->mark) cudaEventDestroy(c->mark);
+    if (c->now) cudaEventDestroy(c->now);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return MPB_OK;
+}
+
+int mpb_context_finish(mpb_context *c, int64_t *elapsed_ns) {
+    if (!c) return fail(MPB_E_INVALID, "ctx is null");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventRecord(c->now, c->stream));
+    CU(cudaEventSynchronize(c->now));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->mark, c->now));
+    if (elapsed_ns) *elapsed_ns = (int64_t)((double)ms * 1e6);
+    CU(cudaEventRecord(c->mark, c->stream));
+    return MPB_OK;
+}
+
+void *mpb_context_stream(mpb_context *c) { return c ? (void *)c->stream : nullptr; }
+int mpb_context_device(mpb_context *c) { return c ? c->device : -1; }
+
+int mpb_buffer_create(mpb_context *c, size_t bytes, mpb_buffer **out) {
+    if (!c || !out) return fail(MPB_E_INVALID, "null argument");
+    *out = nullptr;
+    CU(cudaSetDevice(c->device));
+    mpb_buffer *b = new (std::nothrow) mpb_buffer();
+    if (!b) return fail(MPB_E_NOMEM, "out of host memory");
+    b->ctx = c;
+    b->bytes = bytes;
+    cudaError_t e = cudaMalloc(&b->ptr, bytes ? bytes : 1);
+    if (e != cudaSuccess) { delete b; return fail(MPB_E_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); }
+    *out = b;
+    return MPB_OK;
+}
+
+int mpb_buffer_destroy(mpb_buffer *b) {
+    if (!b) return MPB_OK;
+    cudaSetDevice(b->ctx->device);
+    cudaFree(b->ptr);
+    delete b;
+    return MPB_OK;
+}
+
+int mpb_buffer_copy_from_host(mpb_buffer *b, const void *src, size_t bytes) {
+    if (!b || !src) return fail(MPB_E_INVALID, "null argument");
+    if (bytes > b->bytes) return fail(MPB_E_INVALID, "copy of %zu bytes into a %zu-byte buffer", bytes, b->bytes);
+    CU(cudaSetDevice(b->ctx->device));
+    CU(cudaMemcpyAsync(b->ptr, src, bytes, cudaMemcpyHostToDevice, b->ctx->stream));
+    return MPB_OK;
+}
+
+int mpb_buffer_copy_to_host(mpb_buffer *b, void *dst, size_t bytes) {
+    if (!b || !dst) return fail(MPB_E_INVALID, "null argument");
+    if (bytes > b->bytes) return fail(MPB_E_INVALID, "copy of %zu bytes out of a %zu-byte buffer", bytes, b->bytes);
+    CU(cudaSetDevice(b->ctx->device));
+    CU(cudaMemcpyAsync(dst, b->ptr, bytes, cudaMemcpyDeviceToHost, b->ctx->stream));
+    CU(cudaStreamSynchronize(b->ctx->stream));
+    return MPB_OK;
+}
+
+void *mpb_buffer_device_ptr(mpb_buffer *b) { return b ? b->ptr : nullptr; }
+size_t mpb_buffer_size(mpb_buffer *b) { return b ? b->bytes : 0; }
+
+// ------------------------------------------------------------------ MatrixProfileKernelTLF contract
+static int tlf_check(int dtype, int n, int m, int w, int iteration) {
+    if (dtype != MPB_F64 && dtype != MPB_F32) return fail(MPB_E_INVALID, "dtype must be MPB_F64 or MPB_F32");
+    if (m < 4 || n < m) return fail(MPB_E_INVALID, "need n >= m >= 4 (n=%d, m=%d)", n, m);   // CMakeLists.txt:83-89
+    if (w < 8 || w > n || w >= (1 << 24)) return fail(MPB_E_INVALID, "need 8 <= w <= n (w=%d)", w);   // :83-85
+    if (iteration < 0 || (long long)iteration * w >= (long long)(n - m + 1)) return fail(MPB_E_INVALID, "iteration %d outside [0, ceil((n-m+1)/w))", iteration);
+    return MPB_OK;
+}
+
+int mpb_kernel_tlf_enqueue(mpb_context *c, int dtype, int n, int m, int w, int iteration, const mpb_buffer *input, mpb_buffer *output) {
+    if (!c || !input || !output) return fail(MPB_E_INVALID, "null argument");
+    int rc = tlf_check(dtype, n, m, w, iteration);
+    if (rc != MPB_OK) return rc;
+    const size_t sublen = (size_t)(n - m + 1), esz = dtype == MPB_F64 ? 32 : 16;
+    if (input->bytes < sublen * esz) return fail(MPB_E_INVALID, "input buffer holds %zu bytes, need %zu", input->bytes, sublen * esz);
+    const size_t nRows = sublen - (size_t)iteration * w;
+    if (output->bytes < nRows * esz) return fail(MPB_E_INVALID, "output buffer holds %zu bytes, need %zu", output->bytes, nRows * esz);
+    CU(cudaSetDevice(c->device));
+    const size_t need = mpb::chunk_tlf_scratch_bytes(n, m);
+    if (c->tlf_scratch_bytes < need) {
+        CU(cudaStreamSynchronize(c->stream));
+        if (c->tlf_scratch) cudaFree(c->tlf_scratch);
+        c->tlf_scratch = nullptr; c->tlf_scratch_bytes = 0;
+        CU(cudaMalloc(&c->tlf_scratch, need));
+        c->tlf_scratch_bytes = need;
+    }
+    if (dtype == MPB_F64) CU(mpb::launch_chunk_tlf_f64(n, m, w, iteration, input->ptr, output->ptr, c->tlf_scratch, c->tlf_scratch_bytes, c->stream));
+    else CU(mpb::launch_chunk_tlf_f32(n, m, w, iteration, input->ptr, output->ptr, c->tlf_scratch, c->tlf_scratch_bytes, c->stream));
+    return MPB_OK;
+}
+
+static int tlf_host(int dtype, int n, int m, int w, int iteration, const void *input, void *output) {
+    if (!input || !output) return fail(MPB_E_INVALID, "null argument");
+    int rc = tlf_check(dtype, n, m, w, iteration);
+    if (rc != MPB_OK) return rc;
+    static thread_local mpb_context *ctx = nullptr;   // one implicit context per calling thread, device 0
+    if (!ctx) { rc = mpb_context_create(0, &ctx); if (rc != MPB_OK) return rc; }
+    const size_t sublen = (size_t)(n - m + 1), esz = dtype == MPB_F64 ? 32 : 16;
+    const size_t nRows = sublen - (size_t)iteration * w;
+    mpb_buffer *bin = nullptr, *bout = nullptr;
+    rc = mpb_buffer_create(ctx, sublen * esz, &bin);
+    if (rc == MPB_OK) rc = mpb_buffer_create(ctx, sublen * esz, &bout);
+    if (rc == MPB_OK) rc = mpb_buffer_copy_from_host(bin, input, sublen * esz);
+    if (rc == MPB_OK) rc = mpb_kernel_tlf_enqueue(ctx, dtype, n, m, w, iteration, bin, bout);
+    if (rc == MPB_OK) rc = mpb_buffer_copy_to_host(bout, output, nRows * esz);
+    mpb_buffer_destroy(bin);
+    mpb_buffer_destroy(bout);
+    return rc;
+}
+int mpb_kernel_tlf_f64(int n, int m, int w, int iteration, const void *input, void *output) { return tlf_host(MPB_F64, n, m, w, iteration, input, output); }
+int mpb_kernel_tlf_f32(int n, int m, int w, int iteration, const void *input, void *output) { return tlf_host(MPB_F32, n, m, w, iteration, input, output); }
+
+// ------------------------------------------------------------------ whole-problem engine
+int64_t mpb_useful_cells(int n, int m) {
+    const int64_t L = (int64_t)(n - m + 1) - m / 4;
+    return L > 0 ? L * (L + 1) / 2 : 0;
+}
+
+int mpb_plan_destroy(mpb_plan *p) {
+    if (!p) return MPB_OK;
+    cudaSetDevice(p->ctx->device);
+    cudaStreamSynchronize(p->ctx->stream);
+    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->prof, p->MP, p->corr, p->MPI, p->slow_counter};
+    for (void *q : ptrs) if (q) cudaFree(q);
+    for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
+    delete p;
+    return MPB_OK;
+}
+
+int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb_plan **out) {
+    if (!c || !out) return fail(MPB_E_INVALID, "null argument");
+    *out = nullptr;
+    if (dtype != MPB_F64 && dtype != MPB_F32) return fail(MPB_E_INVALID, "dtype must be MPB_F64 or MPB_F32");
+    if (m < 4 || n < m) return fail(MPB_E_INVALID, "need n >= m >= 4 (n=%d, m=%d)", n, m);
+    if (n - m + 1 <= m / 4) return fail(MPB_E_INVALID, "n-m+1 = %d does not exceed the exclusion zone m/4 = %d: no valid pair", n - m + 1, m / 4);
+    CU(cudaSetDevice(c->device));
+    mpb_plan *p = new (std::nothrow) mpb_plan();
+    if (!p) return fail(MPB_E_NOMEM, "out of host memory");
+    p->ctx = c; p->n = n; p->m = m; p->dtype = dtype; p->flags = flags;
+    p->sublen = n - m + 1; p->excl = m / 4; p->np = mpb::padded_len(p->sublen);
+    const size_t es = dtype == MPB_F64 ? 8 : 4, np = (size_t)p->np;
+#define ALLOC(ptr, bytes)                                                                            \
+    do {                                                                                             \
+        cudaError_t e__ = cudaMalloc((void **)&(ptr), (bytes));                                      \
+        if (e__ != cudaSuccess) { mpb_plan_destroy(p); return fail(MPB_E_NOMEM, "cudaMalloc(%zu) for " #ptr ": %s", (size_t)(bytes), cudaGetErrorString(e__)); } \
+    } while (0)
+    ALLOC(p->T, sizeof(double) * (size_t)n);
+    ALLOC(p->mu, sizeof(double) * (size_t)p->sublen);
+    ALLOC(p->df_dg, 2 * es * np);
+    ALLOC(p->inv, es * np);
+    ALLOC(p->qt0, es * np);
+    ALLOC(p->prof, sizeof(mpb::ProfileEntry) * np);
+    ALLOC(p->MP, sizeof(double) * (size_t)p->sublen);
+    ALLOC(p->corr, sizeof(double) * (size_t)p->sublen);
+    ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
+    ALLOC(p->slow_counter, sizeof(unsigned long long));
+#undef ALLOC
+    // zero padding beyond sublen is what lets tiles run off the matrix edge without bounds checks
+    CU(cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream));
+    CU(cudaMemsetAsync(p->inv, 0, es * np, c->stream));
+    CU(cudaMemsetAsync(p->qt0, 0, es * np, c->stream));
+    CU(cudaMemsetAsync(p->slow_counter, 0, sizeof(unsigned long long), c->stream));
+    for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
+    p->tm.cells = mpb_useful_cells(n, m);
+    *out = p;
+    return MPB_OK;
+}
+
+int mpb_plan_set_shard(mpb_plan *p, int rank, int world) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    if (world < 1 || rank < 0 || rank >= world) return fail(MPB_E_INVALID, "bad shard %d/%d", rank, world);
+    p->rank = rank; p->world = world;
+    return MPB_OK;
+}
+
+int mpb_plan_upload_series(mpb_plan *p, const double *T_host) {
+    if (!p || !T_host) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaEventRecord(p->ev[0], p->ctx->stream));
+    CU(cudaMemcpyAsync(p->T, T_host, sizeof(double) * (size_t)p->n, cudaMemcpyHostToDevice, p->ctx->stream));
+    CU(cudaEventRecord(p->ev[1], p->ctx->stream));
+    p->ran_h2d = true;
+    return MPB_OK;
+}
+
+void *mpb_plan_series_device_ptr(mpb_plan *p) { return p ? p->T : nullptr; }
+
+int mpb_plan_precompute(mpb_plan *p) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaEventRecord(p->ev[2], s));
+    CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, s));
+    if (p->dtype == MPB_F64) CU(mpb::launch_stats_f64(p->T, p->mu, p->n, p->m, (double *)p->df_dg, (double *)p->inv, (double *)p->qt0, s));
+    else CU(mpb::launch_stats_f32(p->T, p->mu, p->n, p->m, (float *)p->df_dg, (float *)p->inv, (float *)p->qt0, s));
+    CU(mpb::launch_profile_init(p->prof, p->np, s));
+    CU(cudaEventRecord(p->ev[3], s));
+    p->tm.launches = 3;
+    return MPB_OK;
+}
+
+int mpb_plan_compute(mpb_plan *p) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaSetDevice(p->ctx->device));
+    mpb::BandLaunch bl;
+    bl.sublen = p->sublen; bl.excl = p->excl; bl.rank = p->rank; bl.world = p->world;
+    bl.strict = (p->flags & MPB_FLAG_STRICT) != 0;
+    bl.slow_counter = p->slow_counter;
+    int ctas = 0;
+    CU(cudaMemsetAsync(p->slow_counter, 0, sizeof(unsigned long long), s));
+    CU(cudaEventRecord(p->ev[4], s));
+    if (p->dtype == MPB_F64) CU(mpb::launch_bands_f64((const double *)p->df_dg, (const double *)p->inv, (const double *)p->qt0, p->prof, bl, &ctas, s));
+    else CU(mpb::launch_bands_f32((const float *)p->df_dg, (const float *)p->inv, (const float *)p->qt0, p->prof, bl, &ctas, s));
+    CU(cudaEventRecord(p->ev[5], s));
+    p->tm.bands = ctas;
+    p->tm.launches += ctas > 0 ? 1 : 0;
+    return MPB_OK;
+}
+
+int mpb_plan_export(mpb_plan *p, void *corr_out, void *index_out) {
+    if (!p || !corr_out || !index_out) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(mpb::launch_export(p->prof, p->sublen, (double *)corr_out, (int32_t *)index_out, p->ctx->stream));
+    p->tm.launches += 1;
+    return MPB_OK;
+}
+
+int mpb_plan_mask_index(mpb_plan *p, const void *corr_max, void *index) {
+    if (!p || !corr_max || !index) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(mpb::launch_mask_index(p->prof, p->sublen, (const double *)corr_max, (int32_t *)index, p->ctx->stream));
+    p->tm.launches += 1;
+    return MPB_OK;
+}
+
+int mpb_plan_import(mpb_plan *p, const void *corr, const void *index) {
+    if (!p || !corr || !index) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(mpb::launch_import(p->prof, p->sublen, (const double *)corr, (const int32_t *)index, p->ctx->stream));
+    p->tm.launches += 1;
+    return MPB_OK;
+}
+
+int mpb_plan_merge_peers(mpb_plan *p, mpb_plan *const *others, int count) {
+    if (!p || (count > 0 && !others)) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    for (int k = 0; k < count; ++k) {
+        mpb_plan *o = others[k];
+        if (!o || o->sublen != p->sublen) return fail(MPB_E_INVALID, "peer plan %d does not match", k);
+        if (o->ctx->device != p->ctx->device) {
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, p->ctx->device, o->ctx->device));
+            if (!can) return fail(MPB_E_CUDA, "device %d cannot access device %d over P2P", p->ctx->device, o->ctx->device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->ctx->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(MPB_E_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+        // the peer's band kernel must be complete before its slots are read
+        CU(cudaSetDevice(o->ctx->device));
+        CU(cudaEventRecord(o->ev[7], o->ctx->stream));
+        CU(cudaSetDevice(p->ctx->device));
+        CU(cudaStreamWaitEvent(p->ctx->stream, o->ev[7], 0));
+        CU(mpb::launch_merge_peer(p->prof, o->prof, p->sublen, p->ctx->stream));
+        p->tm.launches += 1;
+    }
+    return MPB_OK;
+}
+
+int mpb_plan_finalize(mpb_plan *p) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(mpb::launch_finalize(p->prof, p->sublen, p->m, p->MP, p->MPI, p->corr, p->ctx->stream));
+    CU(cudaEventRecord(p->ev[6], p->ctx->stream));
+    p->tm.launches += 1;
+    return MPB_OK;
+}
+
+int mpb_plan_download(mpb_plan *p, double *MP_host, int32_t *MPI_host, double *corr_host) {
+    if (!p || !MP_host || !MPI_host) return fail(MPB_E_INVALID, "null argument");
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaMemcpyAsync(MP_host, p->MP, sizeof(double) * (size_t)p->sublen, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(MPI_host, p->MPI, sizeof(int32_t) * (size_t)p->sublen, cudaMemcpyDeviceToHost, s));
+    if (corr_host) CU(cudaMemcpyAsync(corr_host, p->corr, sizeof(double) * (size_t)p->sublen, cudaMemcpyDeviceToHost, s));
+    CU(cudaEventRecord(p->ev[7], s));
+    CU(cudaStreamSynchronize(s));
+    return MPB_OK;
+}
+
+void *mpb_plan_mp_device_ptr(mpb_plan *p) { return p ? p->MP : nullptr; }
+void *mpb_plan_mpi_device_ptr(mpb_plan *p) { return p ? p->MPI : nullptr; }
+
+int mpb_plan_download_input(mpb_plan *p, void *input_host) {
+    if (!p || !input_host) return fail(MPB_E_INVALID, "null argument");
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaSetDevice(p->ctx->device));
+    const size_t bytes = (size_t)p->sublen * (p->dtype == MPB_F64 ? 32 : 16);
+    void *tmp = nullptr;
+    CU(cudaMalloc(&tmp, bytes));
+    cudaError_t e = p->dtype == MPB_F64
+        ? mpb::launch_pack_input_f64((const double *)p->df_dg, (const double *)p->inv, (const double *)p->qt0, p->sublen, tmp, s)
+        : mpb::launch_pack_input_f32((const float *)p->df_dg, (const float *)p->inv, (const float *)p->qt0, p->sublen, tmp, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(input_host, tmp, bytes, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(tmp);
+    CU(e);
+    return MPB_OK;
+}
+
+int mpb_plan_timings(mpb_plan *p, mpb_timings *out) {
+    if (!p || !out) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaStreamSynchronize(p->ctx->stream));
+    auto span = [&](int a, int b) -> double {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, p->ev[a], p->ev[b]) != cudaSuccess) { cudaGetLastError(); return 0.0; }
+        return (double)ms;
+    };
+    mpb_timings t = p->tm;
+    t.h2d_ms = p->ran_h2d ? span(0, 1) : 0.0;
+    t.precompute_ms = span(2, 3);
+    t.compute_ms = span(4, 5);
+    t.finalize_ms = span(5, 6);
+    t.d2h_ms = span(6, 7);
+    t.total_ms = span(p->ran_h2d ? 0 : 2, 7);
+    unsigned long long slow = 0;
+    CU(cudaMemcpy(&slow, p->slow_counter, sizeof slow, cudaMemcpyDeviceToHost));
+    t.slow_updates = (int64_t)slow;
+    *out = t;
+    return MPB_OK;
+}
+
+int mpb_compute(mpb_context *c, const double *T, int n, int m, int dtype, unsigned flags, double *MP, int32_t *MPI, mpb_timings *timings) {
+    if (!c || !T || !MP || !MPI) return fail(MPB_E_INVALID, "null argument");
+    mpb_plan *p = nullptr;
+    int rc = mpb_plan_create(c, n, m, dtype, flags, &p);
+    if (rc == MPB_OK) rc = mpb_plan_upload_series(p, T);
+    if (rc == MPB_OK) rc = mpb_plan_precompute(p);
+    if (rc == MPB_OK) rc = mpb_plan_compute(p);
+    if (rc == MPB_OK) rc = mpb_plan_finalize(p);
+    if (rc == MPB_OK) rc = mpb_plan_download(p, MP, MPI, nullptr);
+    if (rc == MPB_OK && timings) rc = mpb_plan_timings(p, timings);
+    mpb_plan_destroy(p);
+    return rc;
+}
+
+int mpb_measure_fma_peak(mpb_context *c, int dtype, int iters, double *fma_per_s, double *ms_out) {
+    if (!c || !fma_per_s) return fail(MPB_E_INVALID, "null argument");
+    if (iters < 1) return fail(MPB_E_INVALID, "iters must be positive");
+    CU(cudaSetDevice(c->device));
+    double *sink = nullptr;
+    CU(cudaMalloc(&sink, sizeof(double)));
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    const int blocks = c->sm_count * 8;
+    CU(mpb::launch_fma_peak(dtype, iters / 8 + 1, blocks, sink, c->stream));   // warm-up
+    CU(cudaEventRecord(a, c->stream));
+    CU(mpb::launch_fma_peak(dtype, iters, blocks, sink, c->stream));
+    CU(cudaEventRecord(b, c->stream));
+    CU(cudaEventSynchronize(b));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(sink);
+    const double fmas = (double)blocks * mpb::fma_peak_threads() * mpb::fma_peak_chains() * (double)iters;
+    *fma_per_s = fmas / ((double)ms * 1e-3);
+    if (ms_out) *ms_out = ms;
+    return MPB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,271 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA engine, called through the C ABI
+(include/mp_b200.h via the ctypes binding), against the CPU oracle and the golden vectors that the
+reference's own sources produced.  Tolerances (BASELINE.json north_star): fp64 1e-9 relative on the
+profile, index exact except ties within that tolerance; fp32 1e-4."""
+import numpy as np
+import pytest
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+KAT = ["small128_m16_w32_t16", "b1024_m16_w32_t16", "b1024_m16_w256_t128", "b1024_m32_w512_t128",
+       "b1024_m30_w64_t16", "b16384_m128_w1024_t128"]
+SYN = ["walk4096_m64_w256_t128", "walk8192_m100_w1024_t256"]
+BIG = ["walk65536_m256_w4096_t128", "unif65536_m256_w4096_t128"]
+RTOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def mp():
+    import mpb200
+    assert mpb200.device_count() >= 1
+    return mpb200
+
+
+@pytest.fixture(scope="module")
+def ctx(mp):
+    c = mp.Context(0)
+    yield c
+    c.close()
+
+
+def run_plan(mp, ctx, T, m, dtype=0, flags=0, shard=None):
+    plan = mp.Plan(ctx, T.size, m, dtype, flags)
+    if shard:
+        plan.set_shard(*shard)
+    plan.upload_series(T)
+    plan.precompute()
+    plan.compute()
+    return plan
+
+
+def check_profile(oracle, T, m, corr, MPI, MP, g_corr, g_MPI, rtol=RTOL):
+    """value within rtol (relative) on the correlation, and on the distance after the 1/(2(1-P)) amplification
+    that the Pearson -> distance map applies; index equal, or the two candidates' exact (long double)
+    correlations within the tolerance of each other."""
+    assert g_corr.min() > 0                      # the P=0 clamp is never what is being compared
+    assert (np.abs(corr - g_corr) / np.abs(g_corr)).max() <= rtol
+    g_MP = np.sqrt(2 * m * (1 - g_corr))
+    ok = (1 - g_corr) > 1e-6
+    assert (np.abs(MP - g_MP)[ok] / g_MP[ok]).max() <= rtol
+    bad = np.nonzero(MPI != g_MPI)[0]
+    for i in bad:
+        a, b = oracle.exact_corr(T, m, i, MPI[i]), oracle.exact_corr(T, m, i, g_MPI[i])
+        assert abs(a - b) <= rtol * max(abs(a), abs(b)), (i, MPI[i], g_MPI[i], a, b)
+    return len(bad)
+
+
+@pytest.mark.parametrize("name", KAT + SYN + BIG)
+def test_precompute_bit_exact(mp, ctx, oracle, name):
+    """kernel (1) == PreComputeStatistics, bit for bit (incl. the sequential running mean)."""
+    g = load_golden(name)
+    T, m = g["T"], g["m"]
+    plan = mp.Plan(ctx, T.size, m)
+    plan.upload_series(T)
+    plan.precompute()
+    got = plan.download_input()
+    want = g["input"] if "input" in g else oracle.precompute(T, m)
+    assert got.tobytes() == want.tobytes()
+    plan.close()
+
+
+def _check_chunks(mp, g, inp, out, kind_prefix="vanilla"):
+    T, m, w = g["T"], g["m"], g["w"]
+    n = T.size
+    for it in range((n - m + w) // w):
+        mp.MatrixProfileKernelTLF(n, m, it, inp, out, w=w)
+        nr = n - m + 1 - it * w
+        assert np.array_equal(out["rowAggregate"]["value"][:nr], g[f"{kind_prefix}_chunk{it}_rv"]), it
+        assert np.array_equal(out["rowAggregate"]["index"][:nr], g[f"{kind_prefix}_chunk{it}_ri"]), it
+        assert np.array_equal(out["columnAggregate"]["value"][:nr], g[f"{kind_prefix}_chunk{it}_cv"]), it
+        assert np.array_equal(out["columnAggregate"]["index"][:nr], g[f"{kind_prefix}_chunk{it}_ci"]), it
+
+
+@pytest.mark.parametrize("name", [n for n in KAT if n != "b16384_m128_w1024_t128"])
+def test_tlf_chunks_bit_exact(mp, oracle, name):
+    """MatrixProfileKernelTLF contract: per-chunk OutputDataPacks equal the reference Vanilla kernel's,
+    values and indices (P=0 clamp and tie order included)."""
+    g = load_golden(name)
+    inp = oracle.precompute(g["T"], g["m"])
+    _check_chunks(mp, g, inp, np.zeros(inp.size, mp.OUT_F64))
+
+
+@pytest.mark.parametrize("name", ["f32_b1024_m16_w256_t128", "f32_walk4096_m64_w256_t128"])
+def test_tlf_chunks_bit_exact_float(mp, name):
+    g = load_golden(name)
+    inp = np.ascontiguousarray(g["input"])
+    _check_chunks(mp, g, inp, np.zeros(inp.size, mp.OUT_F32))
+
+
+@pytest.mark.parametrize("name", KAT)
+def test_reference_harness_flow_through_tlf(mp, oracle, name):
+    """The reference's TestMatrixProfileKernel flow (test/include/MatrixProfileTests.hpp:141-213) with the
+    GPU kernel plugged in: chunk loop, UpdateAggregates, PostCompute, then its own pass criterion
+    (|dMP| <= 1e-8 on the distance, identical index) against its independent SCAMP."""
+    g = load_golden(name)
+    T, m, w = g["T"], g["m"], g["w"]
+    n = T.size
+    sublen = n - m + 1
+    inp = oracle.precompute(T, m)
+    out = np.zeros(sublen, mp.OUT_F64)
+    rv = np.full(sublen, -1e12); ri = np.full(sublen, -1, np.int32)
+    cv = np.full(sublen, -1e12); ci = np.full(sublen, -1, np.int32)
+    for it in range((n - m + w) // w):
+        mp.MatrixProfileKernelTLF(n, m, it, inp, out, w=w)
+        off, nr = it * w, sublen - it * w
+        a, b = out["rowAggregate"][:nr], out["columnAggregate"][:nr]
+        k = a["value"] > rv[:nr]; rv[:nr][k] = a["value"][k]; ri[:nr][k] = a["index"][k]
+        k = b["value"] > cv[off:]; cv[off:][k] = b["value"][k]; ci[off:][k] = b["index"][k]
+    pick = rv > cv
+    MP = np.sqrt(2 * m * (1 - np.where(pick, rv, cv)))
+    MPI = np.where(pick, ri, ci)
+    assert np.abs(MP - g["scamp_MP"]).max() <= 1e-8
+    assert np.array_equal(MPI, g["scamp_MPI"])
+    assert np.array_equal(MP, g["vanilla_MP"])     # and bit-identical to the reference kernel's own result
+
+
+@pytest.mark.parametrize("flags", [0, 1])
+@pytest.mark.parametrize("name", KAT + SYN + BIG)
+def test_fast_path_vs_reference_kernels(mp, ctx, oracle, name, flags):
+    """Kernels (1)-(3) vs the reference kernels' merged result. flags=1 (MPB_FLAG_STRICT, un-fused chain)
+    must reproduce the reference's bits; the default nested-FMA chain must stay within 1e-9 relative."""
+    g = load_golden(name)
+    T, m = g["T"], g["m"]
+    plan = run_plan(mp, ctx, T, m, mp.F64, flags)
+    plan.finalize()
+    MP, MPI, corr = plan.download()
+    plan.close()
+    if flags == mp.FLAG_STRICT:
+        assert np.array_equal(corr, g["vanilla_corr"])
+        assert np.array_equal(MP, np.sqrt(2 * m * (1 - g["vanilla_corr"])))
+    nbad = check_profile(oracle, T, m, corr, MPI, MP, g["vanilla_corr"], g["vanilla_MPI"])
+    if flags == mp.FLAG_STRICT and name != "small128_m16_w32_t16":
+        assert nbad == 0
+
+
+def test_one_call_host_api(mp, oracle):
+    g = load_golden("walk8192_m100_w1024_t256")
+    MP, MPI, t = mp.matrix_profile(g["T"], g["m"], return_timings=True)
+    assert np.allclose(MP, np.sqrt(2 * g["m"] * (1 - g["vanilla_corr"])), rtol=1e-9, atol=0)
+    assert np.array_equal(MPI, g["vanilla_MPI"])
+    assert t["cells"] == mp.useful_cells(8192, 100) and t["launches"] >= 5 and t["bands"] >= 1
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_band_shards_merge_to_unsharded_result(mp, ctx, world):
+    """Multi-GPU path on one device: each rank's plan walks bands b % world == rank; the peer merge
+    (exact (corr, index) max) must reproduce the single-plan profile bit for bit."""
+    g = load_golden("walk65536_m256_w4096_t128")
+    T, m = g["T"], g["m"]
+    full = run_plan(mp, ctx, T, m)
+    full.finalize()
+    MP0, MPI0, corr0 = full.download()
+    plans = [run_plan(mp, ctx, T, m, shard=(r, world)) for r in range(world)]
+    plans[0].merge_peers(plans[1:])
+    plans[0].finalize()
+    MP, MPI, corr = plans[0].download()
+    assert np.array_equal(corr, corr0) and np.array_equal(MPI, MPI0) and np.array_equal(MP, MP0)
+    for p in plans + [full]:
+        p.close()
+
+
+def test_export_mask_import_roundtrip(mp, ctx):
+    """The NCCL-merge building blocks (export -> [all-reduce] -> mask -> [all-reduce] -> import) on one
+    device with torch doing the reductions of two shards."""
+    import torch
+    g = load_golden("walk8192_m100_w1024_t256")
+    T, m = g["T"], g["m"]
+    sublen = T.size - m + 1
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    plans = [run_plan(mp, ctx, T, m, shard=(r, 2)) for r in range(2)]
+    with torch.cuda.stream(stream):
+        corr = [torch.empty(sublen, dtype=torch.float64, device="cuda") for _ in plans]
+        idx = [torch.empty(sublen, dtype=torch.int32, device="cuda") for _ in plans]
+        for p, c, i in zip(plans, corr, idx):
+            p.export(c.data_ptr(), i.data_ptr())
+        cmax = torch.maximum(corr[0].view(torch.int64), corr[1].view(torch.int64)).view(torch.float64)
+        for p, i in zip(plans, idx):
+            p.mask_index(cmax.data_ptr(), i.data_ptr())
+        imin = torch.minimum(idx[0], idx[1])
+        plans[0].import_(cmax.data_ptr(), imin.data_ptr())
+        plans[0].finalize()
+        stream.synchronize()
+    MP, MPI, c = plans[0].download()
+    assert np.array_equal(c, g["vanilla_corr"]) or np.abs(c - g["vanilla_corr"]).max() < 1e-12
+    assert np.array_equal(MPI, g["vanilla_MPI"])
+    for p in plans:
+        p.close()
+
+
+def test_full_size_properties(mp, ctx, oracle):
+    """BASELINE.json headline size (n=2^20, m=256, fp64): size-independent properties.
+    (a) the neighbour's own best is at least as good: corr[MPI[i]] >= corr[i] (the same cell feeds both);
+    (b) no neighbour inside the exclusion zone; (c) sampled rows agree with exact long-double
+    correlations; (d) a two-shard run merges to the same bits."""
+    from oracle_py import uniform_series
+    n, m = 1 << 20, 256
+    T = uniform_series(n, 99)
+    plan = run_plan(mp, ctx, T, m)
+    plan.finalize()
+    MP, MPI, corr = plan.download()
+    assert (MPI >= 0).all() and (MPI < n - m + 1).all()
+    assert (corr[MPI] >= corr).all()
+    assert (np.abs(MPI - np.arange(n - m + 1)) >= m // 4).all()
+    assert np.array_equal(MP, np.sqrt(2 * m * (1 - corr)))
+    rows = np.linspace(0, n - m, 48).astype(int)
+    err = max(abs(oracle.exact_corr(T, m, i, MPI[i]) - corr[i]) / corr[i] for i in rows)
+    assert err < 1e-9
+    a, b = (run_plan(mp, ctx, T, m, shard=(r, 2)) for r in range(2))
+    a.merge_peers([b]); a.finalize()
+    MP2, MPI2, corr2 = a.download()
+    assert np.array_equal(corr2, corr) and np.array_equal(MPI2, MPI)
+    for p in (plan, a, b):
+        p.close()
+
+
+def test_fast_path_float_vs_double_oracle(mp, ctx, oracle):
+    """fp32 engine vs the DOUBLE reference kernels at 1e-4 absolute on correlation;
+    the reference's own float path is untested upstream."""
+    g = load_golden("walk8192_m100_w1024_t256")
+    T, m = g["T"], g["m"]
+    plan = run_plan(mp, ctx, T, m, mp.F32)
+    plan.finalize()
+    MP, MPI, corr = plan.download()
+    plan.close()
+    assert np.abs(corr - g["vanilla_corr"]).max() <= 1e-4
+    for i in np.nonzero(MPI != g["vanilla_MPI"])[0]:
+        a, b = oracle.exact_corr(T, m, i, MPI[i]), oracle.exact_corr(T, m, i, g["vanilla_MPI"][i])
+        assert abs(a - b) <= 1e-4
+
+
+def test_edge_shapes(mp, ctx, oracle):
+    """Smallest legal problems, a single partial band, m not a multiple of 4."""
+    rng = np.random.default_rng(3)
+    for n, m in [(24, 8), (64, 8), (200, 30), (1100, 16), (1500, 5), (3000, 64)]:
+        T = np.cumsum(rng.standard_normal(n))
+        w = 8
+        while w * 2 <= min(n, 4096):
+            w *= 2
+        eMP, eMPI, ecorr, _ = oracle.run(T, m, w)
+        plan = run_plan(mp, ctx, T, m, mp.F64, mp.FLAG_STRICT)
+        plan.finalize()
+        MP, MPI, corr = plan.download()
+        plan.close()
+        pos = ecorr > 0      # rows with no positive neighbour keep the kernels' P=0 floor (index then arbitrary upstream, -1 here)
+        assert np.array_equal(corr[pos], ecorr[pos]) and np.array_equal(MPI[pos], eMPI[pos]), (n, m)
+        assert (corr[~pos] == 0).all() and (MPI[~pos] == -1).all()
+
+
+def test_error_behaviour(mp, ctx):
+    with pytest.raises(mp.MpbError):
+        mp.Plan(ctx, 100, 200)               # m > n (reference: CMakeLists.txt:86-89 rejects it at configure time)
+    with pytest.raises(mp.MpbError):
+        mp.Plan(ctx, 16, 16)                 # n-m+1 inside the exclusion zone
+    with pytest.raises(mp.MpbError):
+        mp.Context(10_000)
+    inp = np.zeros(1024 - 16 + 1, mp.IN_F64)
+    out = np.zeros(1024 - 16 + 1, mp.OUT_F64)
+    with pytest.raises(mp.MpbError):
+        mp.MatrixProfileKernelTLF(1024, 16, 99, inp, out, w=32)    # iteration out of range
+    with pytest.raises(mp.MpbError):
+        mp.MatrixProfileKernelTLF(1024, 16, 0, inp, out, w=4)      # w < 8 (row-reduce lanes, Vanilla.cpp:29-36)
