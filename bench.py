@@ -265,7 +265,7 @@ def run_gpu_arm(args):
             pass
         my_cells = cells / world                                   # round-robin bands: equal shares to within one band
         ops = 4.0 * my_cells / (band_ms * 1e-3)
-        prof_path = os.path.join(ROOT, "profiles", "band_kernel_traffic.json")
+        prof_path = os.path.join(ROOT, "profiles", "tile_kernel_traffic.json")
         traffic = None
         if os.path.exists(prof_path):
             traffic = json.load(open(prof_path)).get(f"{args.dtype}_n{n}_m{m}")
@@ -275,7 +275,7 @@ def run_gpu_arm(args):
                "data": "synthetic", "config": workload_config(args),
                "e2e": {"value": cells / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 12 * sublen},
                "gpu_launches": launches,
-               "roofline": {"bound": "fp64_fma_pipe" if args.dtype == "f64" else "fp32_fma_pipe", "kernel": "band_kernel",
+               "roofline": {"bound": "fp64_fma_pipe" if args.dtype == "f64" else "fp32_fma_pipe", "kernel": "tile_kernel",
                             "achieved": ops / 1e12, "peak": fma_peak / 1e12, "unit": "T pipe-ops/s (4 per cell: 2 FMA + 2 MUL)",
                             "frac": ops / fma_peak, "peak_source": "DFMA/FFMA issue-rate microbenchmark measured in this run (mpb_measure_fma_peak)",
                             "kernel_ms": band_ms, "kernel_share_of_step": band_ms / ms_dev, "traffic": traffic,

@@ -32,8 +32,12 @@ extern "C" {
 #define MPB_F64 0
 #define MPB_F32 1
 
-/* mpb_plan flags */
-#define MPB_FLAG_STRICT 1u  /* un-fused QT update (mul,mul,add,add): bit-identical to the reference chain, 6 instead of 4 FP64 ops per cell */
+/* mpb_plan flags.  Default (0) is the fast path: exact window means, nested-FMA QT update, and an exact
+ * fp64 re-seed of every diagonal each `segment rows` rows (bounds drift; BASELINE.json north_star). */
+#define MPB_FLAG_STRICT 1u     /* chain-faithful: implies SEQ_MEAN | NO_RESEED and the un-fused QT update (mul,mul,add,add):
+                                  bit-identical to the reference kernels' chain, 6 instead of 4 FP64 ops per cell */
+#define MPB_FLAG_SEQ_MEAN 2u   /* mu by the reference's sequential running-mean recurrence (HostSideComputation.hpp:29) */
+#define MPB_FLAG_NO_RESEED 4u  /* one full-length chain per diagonal, seeded at row 0 only (Vanilla.cpp:43-55) */
 
 typedef struct mpb_context mpb_context; /* replaces OpenCL::Context   (OpenCL.hpp:73-107, 294-317) */
 typedef struct mpb_buffer mpb_buffer;   /* replaces OpenCL::Buffer<T> (OpenCL.hpp:109-211) */
@@ -92,6 +96,8 @@ typedef struct {
     int64_t slow_updates; /* profile updates that went through the exact 128-bit CAS path */
     int32_t launches;     /* kernels launched by the last run */
     int32_t bands;        /* diagonal bands this rank walked */
+    int32_t items;        /* (band, row segment) work items = CTAs of the tile kernel */
+    int32_t segment_rows; /* rows per re-seeded segment (0 = full-length chains) */
 } mpb_timings;
 
 /* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised
@@ -106,6 +112,9 @@ int mpb_plan_destroy(mpb_plan *plan);
 /* Diagonal-band shard: this plan walks bands b with b % world == rank (the reference's round-robin of
  * chunks over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:101-128). Default (0, 1). */
 int mpb_plan_set_shard(mpb_plan *plan, int rank, int world);
+/* Rows per re-seeded segment (multiple of 256; 0 = never re-seed; negative = choose automatically, the default). */
+int mpb_plan_set_segment_rows(mpb_plan *plan, int rows);
+int mpb_plan_segment_rows(mpb_plan *plan);
 int mpb_plan_upload_series(mpb_plan *plan, const double *T_host);   /* async H2D of T[n] */
 void *mpb_plan_series_device_ptr(mpb_plan *plan);                   /* double[n] in HBM, caller may fill it */
 int mpb_plan_precompute(mpb_plan *plan);                            /* kernel (1) */

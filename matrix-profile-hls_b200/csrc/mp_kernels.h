@@ -2,29 +2,36 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <vector>
 
 namespace mpb {
 struct ProfileEntry;
 
 // kernel (1): precompute.cu
-cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream_t s);
+cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream_t s);      // the reference's sequential running mean
+cudaError_t launch_mu_window(const double *T, int n, int m, double *mu, cudaStream_t s);    // exact window means (parallel)
 cudaError_t launch_stats_f64(const double *T, const double *mu, int n, int m, double *df_dg, double *inv, double *qt0, cudaStream_t s);
 cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, float *df_dg, float *inv, float *qt0, cudaStream_t s);
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s);
 cudaError_t launch_pack_input_f64(const double *df_dg, const double *inv, const double *qt0, int sublen, void *out, cudaStream_t s);
 cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const float *qt0, int sublen, void *out, cudaStream_t s);
 
-// kernel (2): scamp_diag.cu -- diagonal bands [excl + b*BAND_W, ...) for b = rank, rank+world, ...
-struct BandLaunch {
-    int sublen, excl, rank, world;
-    bool strict;
-    unsigned long long *slow_counter;   // device counter of exact-path updates (may be null)
+// kernel (2): scamp_tile.cu -- work items = (diagonal band of BAND_W, row segment of seg_rows); bands b = rank, rank+world, ...
+struct TileLaunch {
+    int n, m, sublen, excl, rank, world;
+    int seg_rows;                       // rows per re-seeded segment (multiple of TILE_H); 0 = one full-length chain per diagonal
+    bool strict;                        // un-fused QT update (the reference's rounding sequence)
+    const double *series, *mu;          // T[n], mu[sublen] (re-seed operands)
+    const int *item_start;              // device: prefix table, nlb + 1 entries
+    int nlb;                            // this rank's band count
+    long long items;                    // total work items (= grid size)
+    unsigned long long *slow_counter;   // device counter of cold-path profile updates (may be null)
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
-cudaError_t launch_bands_f64(const double *df_dg, const double *inv, const double *qt0, ProfileEntry *prof,
-                             const BandLaunch &p, int *launched_ctas, cudaStream_t s);
-cudaError_t launch_bands_f32(const float *df_dg, const float *inv, const float *qt0, ProfileEntry *prof,
-                             const BandLaunch &p, int *launched_ctas, cudaStream_t s);
+long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);
+int default_seg_rows(int sublen, int excl, int m, int world, int sm_count);
+cudaError_t launch_tiles_f64(const double *df_dg, const double *inv, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+cudaError_t launch_tiles_f32(const float *df_dg, const float *inv, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 
 // kernel (3): merge.cu
 cudaError_t launch_finalize(const ProfileEntry *prof, int sublen, int m, double *MP, int32_t *MPI, double *corr, cudaStream_t s);

@@ -77,6 +77,31 @@ mu_scan_kernel(const double *__restrict__ T, int n, int m, double *__restrict__ 
 }
 
 // ---------------------------------------------------------------------------------------------
+// Exact window means (default mode): mu_i = (sum_k T[i+k]) / m, one thread per subsequence, k in order.
+// Unlike the running recurrence above this has no sequential chain (0.1 ms instead of 20 ms at n = 2^20)
+// and no drift: |mu_i - exact| <= m * eps * max|T| instead of growing with i.  The fast path re-seeds QT
+// from exact dot products anyway, so its parity budget against the reference (1e-9) already contains the
+// reference's own running-mean drift (SURVEY.md section 7 "hard parts", App. B-9 (iii)).
+// ---------------------------------------------------------------------------------------------
+constexpr int MUW_THREADS = 256;
+__global__ void __launch_bounds__(MUW_THREADS)
+mu_window_kernel(const double *__restrict__ T, int n, int m, double *__restrict__ mu) {
+    extern __shared__ double sm[];
+    const int sublen = n - m + 1;
+    const int i0 = blockIdx.x * MUW_THREADS;
+    for (int k = threadIdx.x; k < MUW_THREADS + m; k += MUW_THREADS) sm[k] = (i0 + k < n) ? T[i0 + k] : 0.0;
+    __syncthreads();
+    const int i = i0 + threadIdx.x;
+    if (i >= sublen) return;
+    const double *w = sm + threadIdx.x;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;     // 4 interleaved partial sums: shorter chains, smaller error
+    int k = 0;
+    for (; k + 3 < m; k += 4) { s0 += w[k]; s1 += w[k + 1]; s2 += w[k + 2]; s3 += w[k + 3]; }
+    for (; k < m; ++k) s0 += w[k];
+    mu[i] = ((s0 + s1) + (s2 + s3)) / (double)m;
+}
+
+// ---------------------------------------------------------------------------------------------
 // df, dg, QT seeds, inverse norms.  One thread per subsequence, k-loop in the reference's order.
 // ---------------------------------------------------------------------------------------------
 constexpr int STATS_THREADS = 256;
@@ -134,6 +159,17 @@ __global__ void pack_input_kernel(const OutT *__restrict__ df_dg, const OutT *__
 
 cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream_t s) {
     mu_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(T, n, m, mu);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mu_window(const double *T, int n, int m, double *mu, cudaStream_t s) {
+    const int sublen = n - m + 1;
+    const size_t smem = sizeof(double) * (size_t)(MUW_THREADS + m);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(mu_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    mu_window_kernel<<<(sublen + MUW_THREADS - 1) / MUW_THREADS, MUW_THREADS, smem, s>>>(T, n, m, mu);
     return cudaGetLastError();
 }
 

@@ -60,6 +60,12 @@ struct mpb_plan {
     double *MP = nullptr, *corr = nullptr;
     int32_t *MPI = nullptr;
     unsigned long long *slow_counter = nullptr;
+    int seg_rows = -1;                    // requested (-1 = auto)
+    int seg_rows_eff = 0;                 // in effect for the current table
+    int *item_start = nullptr;            // device prefix table of work items
+    int nlb = 0;
+    long long items = 0;
+    bool table_dirty = true;
     cudaEvent_t ev[8] = {};
     mpb_timings tm = {};
     bool ran_h2d = false;
@@ -68,7 +74,7 @@ struct mpb_plan {
 extern "C" {
 
 const char *mpb_last_error(void) { return g_err; }
-const char *mpb_version(void) { return "mpb200 0.1 (sm_100a; DPT=8, BAND_W=1024, TILE_H=256)"; }
+const char *mpb_version(void) { return "mpb200 0.2 (sm_100a; tile kernel DPT=8, BAND_W=1024, TILE_H=256, re-seeded row segments)"; }
 
 int mpb_device_count(int *count) {
     if (!count) return fail(MPB_E_INVALID, "count is null");
@@ -236,7 +242,7 @@ int mpb_plan_destroy(mpb_plan *p) {
     if (!p) return MPB_OK;
     cudaSetDevice(p->ctx->device);
     cudaStreamSynchronize(p->ctx->stream);
-    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->prof, p->MP, p->corr, p->MPI, p->slow_counter};
+    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start};
     for (void *q : ptrs) if (q) cudaFree(q);
     for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
     delete p;
@@ -252,6 +258,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     CU(cudaSetDevice(c->device));
     mpb_plan *p = new (std::nothrow) mpb_plan();
     if (!p) return fail(MPB_E_NOMEM, "out of host memory");
+    if (flags & MPB_FLAG_STRICT) flags |= MPB_FLAG_SEQ_MEAN | MPB_FLAG_NO_RESEED;
     p->ctx = c; p->n = n; p->m = m; p->dtype = dtype; p->flags = flags;
     p->sublen = n - m + 1; p->excl = m / 4; p->np = mpb::padded_len(p->sublen);
     const size_t es = dtype == MPB_F64 ? 8 : 4, np = (size_t)p->np;
@@ -285,7 +292,32 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
 int mpb_plan_set_shard(mpb_plan *p, int rank, int world) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     if (world < 1 || rank < 0 || rank >= world) return fail(MPB_E_INVALID, "bad shard %d/%d", rank, world);
-    p->rank = rank; p->world = world;
+    p->rank = rank; p->world = world; p->table_dirty = true;
+    return MPB_OK;
+}
+
+int mpb_plan_set_segment_rows(mpb_plan *p, int rows) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    if (rows > 0 && rows % mpb::TILE_H != 0) return fail(MPB_E_INVALID, "segment rows must be a multiple of %d (got %d)", mpb::TILE_H, rows);
+    p->seg_rows = rows < 0 ? -1 : rows; p->table_dirty = true;
+    return MPB_OK;
+}
+
+int mpb_plan_segment_rows(mpb_plan *p) { return p ? p->seg_rows_eff : -1; }
+
+// (band, segment) work-item table of this rank: rebuilt when the shard or the segment length changes.
+static int plan_build_table(mpb_plan *p) {
+    if (!p->table_dirty) return MPB_OK;
+    int seg = 0;
+    if (!(p->flags & MPB_FLAG_NO_RESEED)) seg = p->seg_rows >= 0 ? p->seg_rows : mpb::default_seg_rows(p->sublen, p->excl, p->m, 8 /* nominal rank count: keeps results independent of the GPU count */, p->ctx->sm_count);
+    std::vector<int> tab;
+    const long long items = mpb::build_item_table(p->sublen, p->excl, p->rank, p->world, seg, tab);
+    if (items > 0x7fffffffLL) return fail(MPB_E_INVALID, "%lld work items exceed the grid limit; raise the segment length", items);
+    CU(cudaStreamSynchronize(p->ctx->stream));
+    if (p->item_start) { cudaFree(p->item_start); p->item_start = nullptr; }
+    CU(cudaMalloc((void **)&p->item_start, sizeof(int) * tab.size()));
+    CU(cudaMemcpy(p->item_start, tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice));
+    p->nlb = (int)tab.size() - 1; p->items = items; p->seg_rows_eff = seg; p->table_dirty = false;
     return MPB_OK;
 }
 
@@ -305,8 +337,11 @@ int mpb_plan_precompute(mpb_plan *p) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     cudaStream_t s = p->ctx->stream;
     CU(cudaSetDevice(p->ctx->device));
+    int rc = plan_build_table(p);
+    if (rc != MPB_OK) return rc;
     CU(cudaEventRecord(p->ev[2], s));
-    CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, s));
+    if (p->flags & MPB_FLAG_SEQ_MEAN) CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, s));
+    else CU(mpb::launch_mu_window(p->T, p->n, p->m, p->mu, s));
     if (p->dtype == MPB_F64) CU(mpb::launch_stats_f64(p->T, p->mu, p->n, p->m, (double *)p->df_dg, (double *)p->inv, (double *)p->qt0, s));
     else CU(mpb::launch_stats_f32(p->T, p->mu, p->n, p->m, (float *)p->df_dg, (float *)p->inv, (float *)p->qt0, s));
     CU(mpb::launch_profile_init(p->prof, p->np, s));
@@ -319,18 +354,22 @@ int mpb_plan_compute(mpb_plan *p) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     cudaStream_t s = p->ctx->stream;
     CU(cudaSetDevice(p->ctx->device));
-    mpb::BandLaunch bl;
-    bl.sublen = p->sublen; bl.excl = p->excl; bl.rank = p->rank; bl.world = p->world;
-    bl.strict = (p->flags & MPB_FLAG_STRICT) != 0;
-    bl.slow_counter = p->slow_counter;
-    int ctas = 0;
+    int rc = plan_build_table(p);
+    if (rc != MPB_OK) return rc;
+    mpb::TileLaunch tl;
+    tl.n = p->n; tl.m = p->m; tl.sublen = p->sublen; tl.excl = p->excl; tl.rank = p->rank; tl.world = p->world;
+    tl.seg_rows = p->seg_rows_eff;
+    tl.strict = (p->flags & MPB_FLAG_STRICT) != 0;
+    tl.series = p->T; tl.mu = p->mu;
+    tl.item_start = p->item_start; tl.nlb = p->nlb; tl.items = p->items;
+    tl.slow_counter = p->slow_counter;
     CU(cudaMemsetAsync(p->slow_counter, 0, sizeof(unsigned long long), s));
     CU(cudaEventRecord(p->ev[4], s));
-    if (p->dtype == MPB_F64) CU(mpb::launch_bands_f64((const double *)p->df_dg, (const double *)p->inv, (const double *)p->qt0, p->prof, bl, &ctas, s));
-    else CU(mpb::launch_bands_f32((const float *)p->df_dg, (const float *)p->inv, (const float *)p->qt0, p->prof, bl, &ctas, s));
+    if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->inv, (const double *)p->qt0, p->prof, tl, s));
+    else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->inv, (const float *)p->qt0, p->prof, tl, s));
     CU(cudaEventRecord(p->ev[5], s));
-    p->tm.bands = ctas;
-    p->tm.launches += ctas > 0 ? 1 : 0;
+    p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
+    p->tm.launches += p->items > 0 ? 1 : 0;
     return MPB_OK;
 }
 

@@ -14,11 +14,12 @@ multi-GPU plumbing that needs torch.distributed lives in mpb200.dist.
 """
 import ctypes as C
 import os
+import weakref
 
 import numpy as np
 
 F64, F32 = 0, 1
-FLAG_STRICT = 1
+FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED = 1, 2, 4
 _LIB = None
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # matrix-profile-hls_b200/
 LIB_PATH = os.path.join(_PKG_ROOT, "libmpb200.so")
@@ -43,7 +44,7 @@ class MpbError(RuntimeError):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("precompute_ms", C.c_double), ("compute_ms", C.c_double), ("finalize_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("cells", C.c_int64), ("slow_updates", C.c_int64),
-                ("launches", C.c_int32), ("bands", C.c_int32)]
+                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -53,7 +54,7 @@ EXPORTS = [
     "mpb_last_error", "mpb_version", "mpb_device_count", "mpb_context_create", "mpb_context_destroy", "mpb_context_finish",
     "mpb_context_stream", "mpb_context_device", "mpb_buffer_create", "mpb_buffer_destroy", "mpb_buffer_copy_from_host",
     "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
-    "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_upload_series",
+    "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
     "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_useful_cells", "mpb_measure_fma_peak",
@@ -103,6 +104,7 @@ class Context:
 
     def __init__(self, ordinal=0):
         self._h = C.c_void_p()
+        self._children = weakref.WeakSet()    # plans / buffers must be destroyed before their context
         _chk(lib().mpb_context_create(C.c_int(ordinal), C.byref(self._h)))
 
     def finish(self):
@@ -129,6 +131,8 @@ class Context:
 
     def close(self):
         if self._h:
+            for child in list(self._children):
+                child.close()
             lib().mpb_context_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -146,6 +150,7 @@ class Buffer:
         self.ctx = ctx
         self._h = C.c_void_p()
         _chk(lib().mpb_buffer_create(ctx._h, C.c_size_t(nbytes), C.byref(self._h)))
+        ctx._children.add(self)
         self.nbytes = nbytes
 
     def copy_from_host(self, arr):
@@ -197,9 +202,18 @@ class Plan:
         self.sublen = n - m + 1
         self._h = C.c_void_p()
         _chk(lib().mpb_plan_create(ctx._h, C.c_int(n), C.c_int(m), C.c_int(dtype), C.c_uint(flags), C.byref(self._h)))
+        ctx._children.add(self)
 
     def set_shard(self, rank, world):
         _chk(lib().mpb_plan_set_shard(self._h, C.c_int(rank), C.c_int(world)))
+
+    def set_segment_rows(self, rows):
+        """Rows per re-seeded segment (multiple of 256; 0 = never; -1 = automatic)."""
+        _chk(lib().mpb_plan_set_segment_rows(self._h, C.c_int(rows)))
+
+    @property
+    def segment_rows(self):
+        return lib().mpb_plan_segment_rows(self._h)
 
     def upload_series(self, T):
         T = np.ascontiguousarray(T, dtype=np.float64)

@@ -22,5 +22,5 @@ for n in sizes:
                 MP, MPI, corr = plan.download(); t = plan.timings()
             cps = t["cells"] / (t["compute_ms"] * 1e-3)
             print(json.dumps({"n": n, "data": gname, "mode": label, "pre_ms": round(t["precompute_ms"], 3), "compute_ms": round(t["compute_ms"], 3),
-                              "fin_ms": round(t["finalize_ms"], 3), "cells_per_s": cps, "slow_updates": t["slow_updates"], "bands": t["bands"]}), flush=True)
+                              "fin_ms": round(t["finalize_ms"], 3), "cells_per_s": cps, "slow_updates": t["slow_updates"], "bands": t["bands"], "items": t["items"], "seg_rows": t["segment_rows"]}), flush=True)
             plan.close()
