@@ -112,7 +112,7 @@ int mpb_plan_destroy(mpb_plan *plan);
 /* Diagonal-band shard: this plan walks bands b with b % world == rank (the reference's round-robin of
  * chunks over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:101-128). Default (0, 1). */
 int mpb_plan_set_shard(mpb_plan *plan, int rank, int world);
-/* Rows per re-seeded segment (multiple of 256; 0 = never re-seed; negative = choose automatically, the default). */
+/* Rows per re-seeded segment (multiple of 128; 0 = never re-seed; negative = choose automatically, the default). */
 int mpb_plan_set_segment_rows(mpb_plan *plan, int rows);
 int mpb_plan_segment_rows(mpb_plan *plan);
 int mpb_plan_upload_series(mpb_plan *plan, const double *T_host);   /* async H2D of T[n] */

@@ -22,16 +22,18 @@ template <typename T> struct OutputDataPack { Aggregate<T> rowAggregate, columnA
 static_assert(sizeof(Aggregate<double>) == 16 && sizeof(InputDataPack<double>) == 32 && sizeof(OutputDataPack<double>) == 32, "layout");
 static_assert(sizeof(Aggregate<float>) == 8 && sizeof(InputDataPack<float>) == 16 && sizeof(OutputDataPack<float>) == 16, "layout");
 
-// Geometry of the diagonal-band kernel (scamp_diag.cu). A band is BAND_W consecutive diagonals walked
-// by one CTA from row 0 to the end; DPT diagonals per thread; rows are staged TILE_H at a time.
+// Geometry of the diagonal-tile kernel (scamp_tile.cu). A work item is BAND_W consecutive diagonals x one row
+// segment, walked by one CTA; each of its 4 warps owns WARP_DIAGS diagonals (DPT per lane) and stages its OWN
+// tile of TILE_H rows + the columns they touch, so the warps of a CTA never wait for one another.
 constexpr int DPT = 8;                    // diagonals per thread (register micro-tile width)
 constexpr int BAND_THREADS = 128;         // threads per CTA
 constexpr int BAND_W = DPT * BAND_THREADS;  // 1024 diagonals per band
-constexpr int TILE_H = 256;               // rows staged per tile
-constexpr int COL_WIN = TILE_H + BAND_W + 8;  // columns a tile can touch (+ prefetch slack)
+constexpr int WARP_DIAGS = DPT * 32;      // 256 diagonals per warp
+constexpr int TILE_H = 128;               // rows staged per warp tile
+constexpr int COL_WIN = TILE_H + WARP_DIAGS + 8;  // columns a warp tile can touch (+ the incoming column of the last row)
 constexpr int COL_STRIDE = ((COL_WIN + 7) / 8) | 1;  // entries per residue class, odd => conflict-free staging stores
 // Arrays indexed by subsequence are padded so that tiles may run past n-m+1 without bounds checks.
-constexpr int PAD = BAND_W + 2 * TILE_H + 64;
+constexpr int PAD = BAND_W + 4 * TILE_H + 64;
 
 __host__ __device__ inline int padded_len(int sublen) { return ((sublen + PAD + 63) / 64) * 64; }
 
