@@ -30,6 +30,7 @@ sys.path.insert(0, os.path.join(ROOT, "matrix-profile-hls_b200", "python"))
 
 METRIC = "matrix-profile cell updates/sec"
 UNIT = "cells/s"
+_CAL = {}
 REF_W = 4096          # MP_SIZE_W of the reference's README configuration (README.md:35)
 
 
@@ -96,7 +97,7 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # CPU baseline: the reference's own kernel sources on the host cores (bounded sample of chunks)
 # --------------------------------------------------------------------------------------------------
-def cpu_reference_sample(n, m, kind, target_s=15.0, threads=None, est_rate=1.2e8):
+def cpu_reference_sample(n, m, kind, target_s=15.0, threads=None, est_rate=None):
     """Times the reference's Vanilla kernel (kernel/MatrixProfileKernelVanilla.cpp, compiled unmodified into
     oracle/_ref/libmpref_fast.so with -O3 -march=native; falls back to the C restatement when the reference
     was not compiled here) on one diagonal chunk of width w = 4096 per host thread, chunks chosen so that
@@ -109,6 +110,8 @@ def cpu_reference_sample(n, m, kind, target_s=15.0, threads=None, est_rate=1.2e8
     sublen = n - m + 1
     w = REF_W if n >= 4 * REF_W else 256
     nit = (n - m + w) // w
+    if est_rate is None:
+        est_rate = _CAL.get("rate", 2.0e8)             # cells/s per thread; refined after every sample
     want_rows = max(w, int(target_s * est_rate / w))
     it0 = max(0, min(nit - threads, (sublen - want_rows) // w))
     its = [it for it in range(it0, min(nit, it0 + threads))]
@@ -126,6 +129,7 @@ def cpu_reference_sample(n, m, kind, target_s=15.0, threads=None, est_rate=1.2e8
         list(ex.map(one, its))
     dt = time.perf_counter() - t0
     cells = sum(chunk_useful_cells(n, m, w, it) for it in its)
+    _CAL["rate"] = cells / dt / len(its)
     return {"value": cells / dt, "unit": UNIT, "cores": len(its), "kind": "reference" if use_ref else "port",
             "sample": f"Vanilla kernel, double, w={w}: diagonal chunks {its[0]}..{its[-1]} of {nit} of the same n={n}, m={m} series, "
                       f"one chunk per host thread, {cells:.4g} useful cells in {dt:.1f} s (-O3 -march=native)",
@@ -285,6 +289,7 @@ def run_gpu_arm(args):
                "slow_updates": tm["slow_updates"], "bands_rank0": tm["bands"]}
     plan.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_reference_sample(n, m, args.data, target_s=1.5)          # calibrates the per-thread rate (untimed warm-up)
         cb = cpu_reference_sample(n, m, args.data, target_s=args.ref_seconds)
         cb.pop("seconds", None)
         out["cpu_baseline"] = cb
