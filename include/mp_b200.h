@@ -93,11 +93,12 @@ int mpb_kernel_tlf_f32(int n, int m, int w, int iteration, const void *input, vo
 typedef struct {
     double h2d_ms, precompute_ms, compute_ms, finalize_ms, d2h_ms, total_ms; /* device times (CUDA events) */
     int64_t cells;        /* useful cells L(L+1)/2, L = n-m+1 - m/4 */
-    int64_t slow_updates; /* profile updates that went through the exact 128-bit CAS path */
+    int64_t slow_updates; /* profile slots improved through the exact 128-bit CAS path */
     int32_t launches;     /* kernels launched by the last run */
     int32_t bands;        /* diagonal bands this rank walked */
     int32_t items;        /* (band, row segment) work items = CTAs of the tile kernel */
     int32_t segment_rows; /* rows per re-seeded segment (0 = full-length chains) */
+    int64_t filter_hits;  /* thread-rows (DPT cells each) that passed the QT-domain filter and were checked exactly */
 } mpb_timings;
 
 /* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised

@@ -23,15 +23,30 @@ static_assert(sizeof(Aggregate<double>) == 16 && sizeof(InputDataPack<double>) =
 static_assert(sizeof(Aggregate<float>) == 8 && sizeof(InputDataPack<float>) == 16 && sizeof(OutputDataPack<float>) == 16, "layout");
 
 // Geometry of the diagonal-tile kernel (scamp_tile.cu). A work item is BAND_W consecutive diagonals x one row
-// segment, walked by one CTA; each of its 4 warps owns WARP_DIAGS diagonals (DPT per lane) and stages its OWN
+// segment, walked by one CTA; each of its warps owns WARP_DIAGS diagonals (DPT per lane) and stages its OWN
 // tile of TILE_H rows + the columns they touch, so the warps of a CTA never wait for one another.
-constexpr int DPT = 8;                    // diagonals per thread (register micro-tile width)
-constexpr int BAND_THREADS = 128;         // threads per CTA
-constexpr int BAND_W = DPT * BAND_THREADS;  // 1024 diagonals per band
-constexpr int WARP_DIAGS = DPT * 32;      // 256 diagonals per warp
-constexpr int TILE_H = 128;               // rows staged per warp tile
-constexpr int COL_WIN = TILE_H + WARP_DIAGS + 8;  // columns a warp tile can touch (+ the incoming column of the last row)
-constexpr int COL_STRIDE = ((COL_WIN + 7) / 8) | 1;  // entries per residue class, odd => conflict-free staging stores
+// The three knobs can be overridden at build time (make EXTRA="-DMPB_DPT=16 ...") for tuning runs.
+#ifndef MPB_DPT
+#define MPB_DPT 8
+#endif
+#ifndef MPB_TILE_H
+#define MPB_TILE_H 128
+#endif
+#ifndef MPB_WARPS
+#define MPB_WARPS 4
+#endif
+constexpr int DPT = MPB_DPT;              // diagonals per thread (register micro-tile width): 8 or 16
+constexpr int FWIN = 8;                   // columns per filter window (one threshold test covers FWIN cells)
+constexpr int NWIN = DPT / FWIN;          // filter windows per thread-row
+constexpr int BAND_WARPS = MPB_WARPS;     // warps per CTA
+constexpr int BAND_THREADS = 32 * BAND_WARPS;
+constexpr int WARP_DIAGS = DPT * 32;      // diagonals per warp
+constexpr int BAND_W = WARP_DIAGS * BAND_WARPS;   // diagonals per band (= per CTA)
+constexpr int TILE_H = MPB_TILE_H;        // rows staged per warp tile
+constexpr int COL_WIN = TILE_H + WARP_DIAGS + DPT;   // columns (and filter-window starts) a warp tile can touch
+constexpr int COL_STRIDE = ((COL_WIN + DPT - 1) / DPT) | 1;  // entries per residue class, odd => conflict-free staging stores
+static_assert(DPT == 8 || DPT == 16, "DPT");
+static_assert(TILE_H % DPT == 0 && TILE_H % 32 == 0, "TILE_H");
 // Arrays indexed by subsequence are padded so that tiles may run past n-m+1 without bounds checks.
 constexpr int PAD = BAND_W + 4 * TILE_H + 64;
 

@@ -4,123 +4,111 @@
 // kernel/MatrixProfileKernelTiled.cpp:149-223) and the host-side chunk merge UpdateAggregates
 // (include/host/HostSideComputation.hpp:72-90), fused.
 //
-// Decomposition.  The upper triangle is cut into parallelogram work items: BAND_W = 1024 consecutive
-// diagonals x seg_rows rows.  One CTA walks one item; each of its 4 warps owns 256 of the diagonals and
-// lane l keeps the QT values of DPT = 8 adjacent diagonals in registers, so inside an item every diagonal
-// is one unbroken chain
-//     QT <- fma(df_r, dg_c, fma(df_c, dg_r, QT));   P = (QT * inv_r) * inv_c        (2 DFMA + 2 DMUL)
-// (kernel/MatrixProfileKernelVanilla.cpp:81,84).  The first item of a band starts from the precomputed
-// row-0 seeds QT_0 (:43-55); later items re-seed every diagonal with the exact centred dot product
+// Decomposition.  The upper triangle is cut into parallelogram work items: BAND_W consecutive diagonals x
+// seg_rows rows.  One CTA walks one item; each of its warps owns WARP_DIAGS of the diagonals and lane l
+// keeps the QT values of DPT adjacent diagonals in registers, so inside an item every diagonal is one
+// unbroken chain
+//     QT <- fma(df_r, dg_c, fma(df_c, dg_r, QT))                                      (2 DFMA per cell)
+// (kernel/MatrixProfileKernelVanilla.cpp:81).  The first item of a band starts from the precomputed row-0
+// seeds QT_0 (:43-55); later items re-seed every diagonal with the exact centred dot product
 //     QT(r, c) = sum_k (T[r+k] - mu_r)(T[c+k] - mu_c)
 // computed in fp64 from the series (BASELINE.json north_star: "periodic QT re-seeding to bound drift").
 // With seg_rows = 0 (MPB_FLAG_NO_RESEED / MPB_FLAG_STRICT) a band is a single item and every diagonal is
 // the reference's own chain from row 0 to the end.
-// Items are ordered band-major, so the CTAs that run at the same time work on the same band and
-// different row segments: disjoint rows AND disjoint columns, which keeps the thresholds below fresh.
 //
-// Staging.  Every WARP stages its own tile: TILE_H = 128 rows and the TILE_H + 256 columns they touch, in
+// Max/argmax without touching P.  The reference turns every QT into P = QT * inv_r * inv_c (:84, 2 DMUL per
+// cell) and compares it with the row and column aggregates (:87-96).  Here the comparison is moved to the QT
+// domain: a cell can only improve row r or column c if
+//     QT >= norm_r * norm_c * min(best_r, best_c),        norm = 1 / inv,
+// and for the FWIN = 8 cells a lane holds in one row (8 adjacent columns) that is implied by
+//     QT >= min( (best_r * norm_r) * min_c norm_c ,  norm_r * min_c (best_c * norm_c) )   =: theta(r, window)
+// -- two multiplies per 8 cells instead of two per cell.  Row terms {best_r*norm_r, norm_r} and the window
+// minima {min norm_c, min best_c*norm_c} are staged per tile; the test itself compares the HIGH 32 BITS of
+// max(QT_0..7) and theta as integers (VIMNMX3 tree + ISETP on the ALU pipe; an fp64 compare would be a
+// DSETP on the FP64 pipe).  The staged row terms are scaled by (1 - 2^-18), which more than covers every
+// rounding on the way, so the filter has no false negatives: every cell that beats the current profile
+// passes.  The FP64 pipe therefore carries 2 DFMA per cell + 2 DMUL per 8 cells (2.25 pipe ops per cell
+// against the reference formulation's 4).
+//
+// Hits.  A thread-row that passes the filter parks its DPT QT values in a small per-warp hit buffer and the
+// warp goes straight back to the recurrence.  When enough hits wait (or the item ends) the warp drains the
+// buffer with all lanes in parallel: exact P = (QT * inv_r) * inv_c per cell (:84, the reference's rounding
+// order), exact compare against the live profile slot of the column and -- after a shuffle max over the
+// thread-row -- of the row, and a 128-bit compare-and-swap where it wins (mp_common.cuh: larger corr wins,
+// equal corr -> smaller index; deterministic for any arrival order or GPU count).  The profile (one 16-byte
+// {corr, index} slot per subsequence, row and column roles merged, HostSideComputation.hpp:61) lives in
+// HBM/L2 and is only ever touched by drains and by the per-tile threshold snapshots.
+//
+// Staging.  Every WARP stages its own tile (TILE_H rows and the TILE_H + WARP_DIAGS columns they touch) in
 // its private slice of shared memory, synchronised with __syncwarp only -- there is no CTA-wide barrier in
-// the main loop (ncu of the CTA-shared version showed 48 % of warp time parked at __syncthreads).  Column
-// data is stored de-interleaved by (column mod 8) so that the 32 lanes, whose columns are 8 apart, read
-// consecutive shared-memory words (conflict-free LDS.128).
-//
-// Max/argmax.  The profile (one 16-byte {corr, index} slot per subsequence, row and column roles merged,
-// include/host/HostSideComputation.hpp:61) lives in HBM/L2.  An fp64 compare is a DSETP on the FP64 pipe,
-// so the hot loop never compares doubles.  Each tile snapshots the HIGH 32 BITS of the current best
-// correlation of its rows and columns (for P > 0 the IEEE pattern is monotone; P <= 0 has the sign bit set
-// or is zero and never passes; the profile starts at +0.0, the reference kernels' own P = 0 floor) and, per
-// column, the minimum of that snapshot over the 8-column window that ends there (cm8).  Per thread-row
-// (8 cells) the loop takes max3-trees of hi32(P) (VIMNMX3) and tests it once against
-// min(row threshold, cm8 of the lane's current 8-column window).  Only thread-rows that pass take the
-// cold path: exact per-cell tests, a 128-bit compare-and-swap on the profile slot (mp_common.cuh), and a
-// shared-memory atomicMax that tightens the thresholds for the rest of the warp at once; the profile updates
-// themselves are queued per warp and applied in parallel at tile boundaries (flush_queue).
+// the main loop.  Column data is stored de-interleaved by (column mod DPT) so that the 32 lanes, whose
+// columns are DPT apart, read consecutive shared-memory words (conflict-free LDS.128).
 #include "mp_common.cuh"
 #include "mp_kernels.h"
 
 namespace mpb {
 
-// Shared-memory records: rowA[i] = {df, dg}, rowB[i] = {inv, threshold}; colA[p] = {df, dg},
-// colB[p] = {inv, cm8, exact column threshold}.  Each is fetched with one vector load.
 template <typename T> struct Tr;
-template <> struct Tr<double> {
-    using T2 = double2;
-    struct __align__(16) RowB { double inv; int thr; int pad; };
-    struct __align__(16) ColB { double inv; int cm8; int cthr; };
-    struct RowBV { double inv; int thr; };
-    struct ColV { double inv; int cm8; };
-    static __device__ __forceinline__ RowBV load_rowb(const RowB *r) {
-        const double2 b = *reinterpret_cast<const double2 *>(r);
-        return {b.x, __double2loint(b.y)};
-    }
-    static __device__ __forceinline__ ColV load_colb(const ColB *c) {
-        const double2 b = *reinterpret_cast<const double2 *>(c);
-        return {b.x, __double2loint(b.y)};
-    }
-};
-template <> struct Tr<float> {
-    using T2 = float2;
-    struct __align__(8) RowB { float inv; int thr; };
-    struct __align__(16) ColB { float inv; int cm8; int cthr; int pad; };
-    struct RowBV { float inv; int thr; };
-    struct ColV { float inv; int cm8; };
-    static __device__ __forceinline__ RowBV load_rowb(const RowB *r) {
-        const float2 b = *reinterpret_cast<const float2 *>(r);
-        return {b.x, __float_as_int(b.y)};
-    }
-    static __device__ __forceinline__ ColV load_colb(const ColB *c) {
-        const float2 b = *reinterpret_cast<const float2 *>(c);
-        return {b.x, __float_as_int(b.y)};
-    }
-};
+template <> struct Tr<double> { using T2 = double2; };
+template <> struct Tr<float> { using T2 = float2; };
 
-struct WarpCtx {          // per-warp context the cold path reads back from shared memory
-    ProfileEntry *prof;
-    int r0, c0;           // global row of tile row 0, global column of window column 0
-    unsigned slow;        // profile updates attempted by this warp
-    unsigned qn;          // candidates pushed since the last flush (may exceed QCAP: the excess went straight to HBM)
-};
-static_assert(sizeof(WarpCtx) <= 32, "ctx slot");
-
-// Candidate queue.  A candidate that passed the exact per-cell test is parked here (16 bytes) and the warp
-// goes straight back to the FP64 loop; the 128-bit compare-and-swaps on the profile are issued later, by all
-// lanes in parallel, so their L2 round trips overlap instead of stalling the warp once per candidate
-// (ncu: 28 % of warp time sat in the blocking version of this path).
-struct __align__(16) QEntry { double val; int slot; int idx; };
-constexpr int QCAP = 128;
-constexpr int QFLUSH = 64;    // flush at a tile boundary once this many candidates wait
-
-constexpr int SEED_KC = TILE_H;   // k-chunk of the seed dot products (series samples staged per pass)
-
+#ifndef MPB_RB
+#define MPB_RB 8
+#endif
+constexpr int RB = MPB_RB;                // rows per branch-free block of the hot loop (one vote + branch per block)
+static_assert(DPT % RB == 0, "RB");
+constexpr int HCAP = 48;                  // hit buffer capacity (thread-rows)
+constexpr int HDRAIN = HCAP - 32;         // drain once more than this many hits wait (a row can add up to 32)
+constexpr int SEED_KC = TILE_H;           // k-chunk of the seed dot products (series samples staged per pass)
 constexpr int ROWS_STAGED = TILE_H + 8;   // TILE_H rows + the first row of the next tile (pipelined QT step) + prefetch slack
+constexpr int COL_SLOTS = DPT * COL_STRIDE;
+constexpr unsigned FULL = 0xffffffffu;
 
 template <typename T>
 struct WarpSmem {
     using T2 = typename Tr<T>::T2;
-    using RowB = typename Tr<T>::RowB;
-    using ColB = typename Tr<T>::ColB;
-    static constexpr int BYTES = 32 + ROWS_STAGED * (int)(sizeof(T2) + sizeof(RowB)) + DPT * COL_STRIDE * (int)(sizeof(T2) + sizeof(ColB)) + QCAP * (int)sizeof(QEntry);
-    WarpCtx *ctx; T2 *rowA; RowB *rowB; T2 *colA; ColB *colB; QEntry *queue;
+    static constexpr int BYTES = 2 * ROWS_STAGED * (int)sizeof(T2) + 2 * COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * 4 +
+                                 HCAP * DPT * (int)sizeof(T) + HCAP * 8;
+    T2 *rowA;     // [i] = {df_r, dg_r}
+    T2 *rowB;     // [i] = {best_r * norm_r * s, norm_r * s},  s = 1 - 2^-18
+    T2 *colA;     // [slot(x)] = {df_c, dg_c}
+    T2 *colW;     // [slot(y)] = {min norm_c, min best_c * norm_c} over the window of FWIN columns starting at y
+    int *ck;      // [slot(x)] = filter key of best_c * norm_c (input of the window minimum)
+    T *hitQ;      // [h][DPT] parked QT values
+    int2 *hitM;   // [h] = {row, first column}
     __device__ __forceinline__ explicit WarpSmem(unsigned char *base) {
-        ctx = reinterpret_cast<WarpCtx *>(base);
-        rowA = reinterpret_cast<T2 *>(base + 32);
-        rowB = reinterpret_cast<RowB *>(rowA + ROWS_STAGED);
-        colA = reinterpret_cast<T2 *>(rowB + ROWS_STAGED);
-        colB = reinterpret_cast<ColB *>(colA + DPT * COL_STRIDE);
-        queue = reinterpret_cast<QEntry *>(colB + DPT * COL_STRIDE);
+        rowA = reinterpret_cast<T2 *>(base);
+        rowB = rowA + ROWS_STAGED;
+        colA = rowB + ROWS_STAGED;
+        colW = colA + COL_SLOTS;
+        ck = reinterpret_cast<int *>(colW + COL_SLOTS);
+        hitQ = reinterpret_cast<T *>(ck + COL_SLOTS);
+        hitM = reinterpret_cast<int2 *>(hitQ + HCAP * DPT);
     }
 };
 static_assert(WarpSmem<double>::BYTES % 16 == 0 && WarpSmem<float>::BYTES % 16 == 0, "warp slices stay 16-byte aligned");
-static_assert(ROWS_STAGED * sizeof(float2) >= SEED_KC * sizeof(double), "seed operand A aliases the rowA buffer");
-static_assert(DPT * COL_STRIDE * sizeof(float2) >= (SEED_KC + WARP_DIAGS + DPT) * sizeof(double), "seed window U aliases colA");
+static_assert((ROWS_STAGED * sizeof(float2)) % 16 == 0 && (COL_SLOTS * sizeof(float2)) % 16 == 0 && (COL_SLOTS * 4) % 16 == 0 &&
+              (HCAP * DPT * sizeof(float)) % 16 == 0, "sub-arrays stay 16-byte aligned");
+static_assert(2 * ROWS_STAGED * sizeof(float2) >= SEED_KC * sizeof(double), "seed operand A aliases rowA/rowB");
+static_assert(2 * COL_SLOTS * sizeof(float2) >= COL_SLOTS * sizeof(double), "seed window U aliases colA/colW");
+static_assert(SEED_KC + WARP_DIAGS + DPT <= COL_WIN && SEED_KC % DPT == 0, "seed window fits the column slots");
 
-__device__ __forceinline__ int col_slot(int x) { return (x & 7) * COL_STRIDE + (x >> 3); }
+template <typename T> constexpr int cta_smem_bytes() { return BAND_WARPS * WarpSmem<T>::BYTES; }
+template <typename T> constexpr int ctas_per_sm() {
+    return (227 * 1024) / (cta_smem_bytes<T>() + 1024) < 1 ? 1 : ((227 * 1024) / (cta_smem_bytes<T>() + 1024) > 8 ? 8 : (227 * 1024) / (cta_smem_bytes<T>() + 1024));
+}
 
-// Filter key: monotone in P for P > 0; never passes for P <= 0 (thresholds are >= 1).
-__device__ __forceinline__ int filter_key(double p) { return __double2hiint(p); }
-__device__ __forceinline__ int filter_key(float p) { return __float_as_int(p); }
-__device__ __forceinline__ int threshold_of(double best, double) { const int k = __double2hiint(best); return k < 1 ? 1 : k; }
-__device__ __forceinline__ int threshold_of(double best, float) { const int k = __float_as_int((float)best); return k < 1 ? 1 : k; }
+__device__ __forceinline__ int col_slot(int x) { return (x % DPT) * COL_STRIDE + (x / DPT); }
+
+// Filter key: the high word of the IEEE pattern, monotone for positive values; negative values have the sign
+// bit set (negative as an int) and never pass; NaN (e.g. 0 * inf on zero padding) is a huge positive key,
+// which as a threshold means "never passes".
+__device__ __forceinline__ int key_of(double v) { return __double2hiint(v); }
+__device__ __forceinline__ int key_of(float v) { return __float_as_int(v); }
+__device__ __forceinline__ double slack(double) { return 1.0 - 1.0 / 262144.0; }
+__device__ __forceinline__ float slack(float) { return 1.0f - 1.0f / 262144.0f; }
+__device__ __forceinline__ void set_key(double &dst, int key) { dst = __hiloint2double(key, 0); }
+__device__ __forceinline__ void set_key(float &dst, int key) { dst = __int_as_float(key); }
 
 template <bool STRICT> __device__ __forceinline__ double qt_step(double qt, double dfr, double dgr, double dfc, double dgc) {
     if (STRICT) return __dadd_rn(qt, __dadd_rn(__dmul_rn(dfr, dgc), __dmul_rn(dfc, dgr)));   // the reference's rounding sequence (:81)
@@ -132,62 +120,95 @@ template <bool STRICT> __device__ __forceinline__ float qt_step(float qt, float 
 }
 __device__ __forceinline__ double corr_of(double qt, double ir, double ic) { return __dmul_rn(__dmul_rn(qt, ir), ic); }   // :84
 __device__ __forceinline__ float corr_of(float qt, float ir, float ic) { return __fmul_rn(__fmul_rn(qt, ir), ic); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 
 extern __shared__ __align__(16) unsigned char smem_raw[];
 
 // ---------------------------------------------------------------------------------------------
-// Cold path: thread-row (tile row i, this lane's 8 diagonals) passed the hi32 filter.  Exact per-cell tests
-// against the shared thresholds; survivors are queued and the thresholds raised to the candidate's own key
-// at once (the candidate WILL be applied, so anything below it can be dropped from now on).
+// Drain: applies the parked hits to the profile.  Lane e handles cell e of the buffer (hit e / DPT, diagonal
+// e % DPT), so 32 / DPT hits are resolved per pass with their memory round trips overlapped.  Warp-collective.
+// Returns the number of profile slots this warp actually improved (statistics only).
 // ---------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __forceinline__ void push_candidate(WarpSmem<T> &S, double val, int slot, int idx) {
-    const unsigned pos = atomicAdd(&S.ctx->qn, 1u);
-    if (pos < (unsigned)QCAP) { QEntry e; e.val = val; e.slot = slot; e.idx = idx; S.queue[pos] = e; }
-    else profile_update(S.ctx->prof + slot, val, idx);     // queue full (start-up burst): blocking update
-}
-
-template <typename T>
-__device__ __noinline__ void cold_row(T p0, T p1, T p2, T p3, T p4, T p5, T p6, T p7, int i) {
+__device__ __noinline__ unsigned drain_hits(int nhits, const T *__restrict__ inv, ProfileEntry *prof) {
+    const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
-    const T P[DPT] = {p0, p1, p2, p3, p4, p5, p6, p7};
-    const int x0 = i + DPT * (threadIdx.x & 31);    // window column of diagonal j = 0
-    const int row = S.ctx->r0 + i, c0 = S.ctx->c0;
-    volatile int *rthr_p = &S.rowB[i].thr;
-    const int rthr = *rthr_p;
-    int bestj = -1;
-    T bestp = 0;
+    __syncwarp();
+    unsigned wins = 0;
+    const int ncell = nhits * DPT;
+    for (int base = 0; base < ncell; base += 32) {
+        const int e = base + lane;
+        const bool act = e < ncell;
+        const int h = act ? e / DPT : 0, j = e % DPT;
+        const int2 mt = S.hitM[h];
+        const T q = S.hitQ[h * DPT + j];
+        const int row = mt.x, col = mt.y + j;
+        const T p = corr_of(q, inv[row], inv[col]);
+        double pv = act ? (double)p : -1.0;
+        if (!(pv > 0.0)) pv = -1.0;                          // P <= 0 and NaN never enter the profile (it starts at +0.0)
+        if (pv > 0.0) {
+            const double before = profile_update(prof + col, pv, row);
+            wins += before == pv;
+        }
+        double bv = pv;
+        int bc = col;
 #pragma unroll
-    for (int j = 0; j < DPT; ++j) {
-        const int key = filter_key(P[j]);
-        if (key >= rthr && (bestj < 0 || P[j] > bestp)) { bestj = j; bestp = P[j]; }   // best of the row; ties keep the smaller column
-        volatile int *cp = &S.colB[col_slot(x0 + j)].cthr;
-        if (key >= *cp) {
-            push_candidate<T>(S, (double)P[j], c0 + x0 + j, row);
-            atomicMax((int *)cp, key);
+        for (int s = 1; s < DPT; s <<= 1) {                  // best of the thread-row; ties keep the smaller column
+            const double ov = __shfl_xor_sync(FULL, bv, s);
+            const int oc = __shfl_xor_sync(FULL, bc, s);
+            if (ov > bv || (ov == bv && oc < bc)) { bv = ov; bc = oc; }
+        }
+        if (act && j == 0 && bv > 0.0) {
+            const double before = profile_update(prof + row, bv, bc);
+            wins += before == bv;
         }
     }
-    if (bestj >= 0) {
-        push_candidate<T>(S, (double)bestp, row, c0 + x0 + bestj);
-        atomicMax((int *)rthr_p, filter_key(bestp));
-    }
+    __syncwarp();
+    return wins;
 }
 
-// Applies the queued candidates to the profile: one candidate per lane, all lanes at once. Warp-collective.
-template <typename T>
-__device__ __noinline__ void flush_queue() {
+// ---------------------------------------------------------------------------------------------
+// Replay of one branch-free block.  The hot loop only remembers WHICH of its RB rows passed the filter (one bit
+// per row and lane) and the QT values at the start of the block.  When any lane of the warp has a bit set,
+// the block is walked again from that checkpoint with the same operands in the same order (bit-identical QT),
+// and the flagged thread-rows are parked in the hit buffer.  Warp-collective; returns the new hit count.
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct QVec { T v[DPT]; };
+
+template <typename T, bool STRICT>
+__device__ __noinline__ int replay_block(QVec<T> qc, unsigned hm, int i0, int r0, int c0, int hitcnt, const T *__restrict__ inv,
+                                         ProfileEntry *prof, unsigned *wins) {
+    using T2 = typename Tr<T>::T2;
+    const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
-    __syncwarp();
-    const unsigned pushed = S.ctx->qn;
-    const int nq = pushed < (unsigned)QCAP ? (int)pushed : QCAP;
-    ProfileEntry *prof = S.ctx->prof;
-    for (int e = threadIdx.x & 31; e < nq; e += 32) {
-        const QEntry q = S.queue[e];
-        profile_update(prof + q.slot, q.val, q.idx);
+    const unsigned any = __reduce_or_sync(FULL, hm);
+    const int last = 31 - __clz((int)any);                   // last flagged row of the block (any != 0)
+    for (int t = 0; t <= last; ++t) {
+        const int i = i0 + t;
+        const bool flagged = (hm >> t) & 1u;
+        const unsigned mk = __ballot_sync(FULL, flagged);
+        if (mk) {
+            if (flagged) {
+                const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
+#pragma unroll
+                for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = qc.v[j];
+                S.hitM[pos] = make_int2(r0 + i, c0 + i + DPT * lane);
+            }
+            hitcnt += __popc(mk);
+            if (hitcnt > HDRAIN) { *wins += drain_hits<T>(hitcnt, inv, prof); hitcnt = 0; }
+        }
+        if (t < last) {
+            const T2 ra = S.rowA[i + 1];
+            const int x = i + 1 + DPT * lane;
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                const T2 c = S.colA[col_slot(x + j)];
+                qc.v[j] = qt_step<STRICT>(qc.v[j], ra.x, ra.y, c.x, c.y);
+            }
+        }
     }
-    __syncwarp();
-    if ((threadIdx.x & 31) == 0) { S.ctx->slow += pushed; S.ctx->qn = 0; }
-    __syncwarp();
+    return hitcnt;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -199,8 +220,8 @@ __device__ __noinline__ void flush_queue() {
 template <typename T>
 __device__ __forceinline__ void reseed(T (&qt)[DPT], WarpSmem<T> &S, const double *__restrict__ Tser, const double *__restrict__ mu,
                                        int n, int m, int sublen, int rs, int d0w, int lane) {
-    double *A = reinterpret_cast<double *>(S.rowA);      // aliases the rowA buffer
-    double *U = reinterpret_cast<double *>(S.colA);      // aliases colA (de-interleaved like the columns)
+    double *A = reinterpret_cast<double *>(S.rowA);      // aliases rowA/rowB
+    double *U = reinterpret_cast<double *>(S.colA);      // aliases colA/colW (de-interleaved like the columns)
     const double mur = mu[rs];
     const double muref = mu[min(rs + d0w, sublen - 1)];
     double acc[DPT], sumA = 0.0;
@@ -222,7 +243,7 @@ __device__ __forceinline__ void reseed(T (&qt)[DPT], WarpSmem<T> &S, const doubl
             for (int kk = 0; kk < DPT; ++kk) {
                 const double a = A[K * DPT + kk];
 #pragma unroll
-                for (int j = 0; j < DPT; ++j) acc[j] = fma(a, w[(kk + j) & 7], acc[j]);
+                for (int j = 0; j < DPT; ++j) acc[j] = fma(a, w[(kk + j) % DPT], acc[j]);
                 sumA += a;
                 w[kk] = U[kk * COL_STRIDE + lane + K + 1];
             }
@@ -236,16 +257,24 @@ __device__ __forceinline__ void reseed(T (&qt)[DPT], WarpSmem<T> &S, const doubl
     __syncwarp();   // A/U are about to be overwritten by the first tile
 }
 
+// max of the filter keys of FWIN = 8 values
+template <typename T>
+__device__ __forceinline__ int max_key8(const T *q) {
+    const int a = __vimax3_s32(key_of(q[0]), key_of(q[1]), key_of(q[2]));
+    const int b = __vimax3_s32(key_of(q[3]), key_of(q[4]), key_of(q[5]));
+    const int c = __vimax3_s32(key_of(q[6]), key_of(q[7]), a);
+    return max(b, c);
+}
+
 // item_start[lb] = first work item of this rank's local band lb (nlb + 1 entries)
+// counters[0] += thread-rows that passed the filter, counters[1] += profile slots improved
 template <typename T, bool STRICT>
-__global__ void __launch_bounds__(BAND_THREADS, 3)
-tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const T *__restrict__ inv, const T *__restrict__ qt0,
-            const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
+__global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
+tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ inv,
+            const T *__restrict__ qt0, const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
             const int *__restrict__ item_start, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
-            unsigned long long *counter) {
+            unsigned long long *counters) {
     using T2 = typename Tr<T>::T2;
-    using RowB = typename Tr<T>::RowB;
-    using ColB = typename Tr<T>::ColB;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
 
@@ -268,48 +297,64 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const T *__restrict__ 
     } else {
         reseed<T>(qt, S, Tser, mu, n, m, sublen, rbeg - 1, d0w, lane);
     }
-    if (lane == 0) { S.ctx->prof = prof; S.ctx->slow = 0; S.ctx->qn = 0; }
 
-    // Software pipeline: on entry to row i the registers hold QT(row i) already; the loop body turns it into
-    // P(row i), then issues the QT step of row i+1 BEFORE testing P(row i), so the max-tree / compare / branch
-    // latency of one row hides behind the FMAs of the next.  Each tile therefore stages TILE_H + 1 rows.
+    int hitcnt = 0;                 // warp-uniform: hits parked in the buffer
+    unsigned nhit = 0, nwin = 0;    // statistics
+    const T sl = slack(T(0));
+
+    // Software pipeline: on entry to row i the registers hold QT(row i) already; the loop body takes the filter
+    // keys of QT(row i), then issues the QT step to row i+1 BEFORE branching on the test, so the max-tree /
+    // compare / vote latency of one row hides behind the FMAs of the next.  Each tile stages TILE_H + 1 rows.
     bool first_tile = true;
     for (int r0 = rbeg; r0 < rend; r0 += TILE_H) {
         const int c0 = r0 + d0w;
         __syncwarp();   // previous tile fully consumed
-        if (S.ctx->qn >= (unsigned)QFLUSH) flush_queue<T>();
-        if (lane == 0) { S.ctx->r0 = r0; S.ctx->c0 = c0; }
 #pragma unroll
         for (int i = lane; i < ROWS_STAGED; i += 32) {
             S.rowA[i] = df_dg[r0 + i];
-            RowB rb;
-            rb.inv = inv[r0 + i];
-            rb.thr = threshold_of(__ldcg(&prof[r0 + i].corr), T(0));
+            const T norm = nm[r0 + i].x;
+            const T best = (T)__ldcg(&prof[r0 + i].corr);
+            T2 rb;
+            rb.y = mul_rn(norm, sl);
+            rb.x = mul_rn(best, rb.y);
             S.rowB[i] = rb;
         }
 #pragma unroll 4
         for (int x = lane; x < COL_WIN; x += 32) {
             const int p = col_slot(x);
             S.colA[p] = df_dg[c0 + x];
-            S.colB[p].inv = inv[c0 + x];
-            S.colB[p].cthr = threshold_of(__ldcg(&prof[c0 + x].corr), T(0));
+            const T2 nv = nm[c0 + x];                       // {norm_c, min of norm over [c, c + FWIN)}
+            const T best = (T)__ldcg(&prof[c0 + x].corr);
+            T2 w;
+            w.x = nv.y;
+            w.y = T(0);
+            S.colW[p] = w;
+            S.ck[p] = key_of(mul_rn(best, nv.x));
         }
         __syncwarp();
-        for (int x = DPT + lane; x < COL_WIN; x += 32) {   // cm8[x] = min of the exact thresholds of columns [x-8, x)
-            int mn = S.colB[col_slot(x - 1)].cthr;
+        // window minima of the column keys: lane owns entry q (columns DPT*q .. DPT*q + DPT - 1) and needs entry q + 1
+        for (int q = lane; q < COL_STRIDE; q += 32) {
+            int a[DPT + FWIN];
 #pragma unroll
-            for (int e = 2; e <= DPT; ++e) mn = min(mn, S.colB[col_slot(x - e)].cthr);
-            S.colB[col_slot(x)].cm8 = mn;
+            for (int k = 0; k < DPT; ++k) a[k] = S.ck[k * COL_STRIDE + q];
+#pragma unroll
+            for (int k = 0; k < FWIN; ++k) a[DPT + k] = q + 1 < COL_STRIDE ? S.ck[k * COL_STRIDE + q + 1] : 0x7fffffff;
+#pragma unroll
+            for (int k = 0; k < DPT; ++k) {
+                int mn = a[k];
+#pragma unroll
+                for (int e = 1; e < FWIN; ++e) mn = min(mn, a[k + e]);
+                set_key(S.colW[k * COL_STRIDE + q].y, mn);
+            }
         }
         __syncwarp();
 
-        // column registers: slot k holds window column x = i + 8*lane + ((k - i) mod 8)
-        T cdf[DPT], cdg[DPT], civ[DPT];
+        // column registers: slot k holds window column x = i + DPT*lane + ((k - i) mod DPT)
+        T cdf[DPT], cdg[DPT];
 #pragma unroll
         for (int k = 0; k < DPT; ++k) {
-            const int p = k * COL_STRIDE + lane;
-            const T2 a = S.colA[p];
-            cdf[k] = a.x; cdg[k] = a.y; civ[k] = S.colB[p].inv;
+            const T2 a = S.colA[k * COL_STRIDE + lane];
+            cdf[k] = a.x; cdg[k] = a.y;
         }
         if (first_tile) {                                  // pipeline prologue: QT(row rbeg)
             const T2 ra = S.rowA[0];
@@ -317,43 +362,69 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const T *__restrict__ 
             for (int j = 0; j < DPT; ++j) qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[j], cdg[j]);
             first_tile = false;
         }
-        const T2 *rowA = S.rowA + 1;
-        const RowB *rowB = S.rowB;
+        const T2 *rowA = S.rowA + 2;                       // [ii] = {df, dg} of row i + 2 (consumed one sub-step later)
+        const T2 *rowB = S.rowB + 1;                       // [ii] = threshold terms of row i + 1
         const T2 *colA = S.colA + lane + 1;
-        const ColB *colB = S.colB + lane + 1;
-        typename Tr<T>::RowBV rb = Tr<T>::load_rowb(rowB);
+        const T2 *colW = S.colW + lane;
+        // operands of sub-step 0, loaded one sub-step ahead like all the others
+        T2 ra = S.rowA[1];                                 // {df, dg} of row i + 1
+        T2 rb = S.rowB[0];                                 // threshold terms of row i
+        T2 nd = colA[0];                                   // column entering the lane's window: x = i + DPT*lane + DPT
+        T2 cw[NWIN];                                       // window terms of row i: start y = i + DPT*lane + FWIN*w
+#pragma unroll
+        for (int w = 0; w < NWIN; ++w) cw[w] = colW[((FWIN * w) % DPT) * COL_STRIDE + (FWIN * w) / DPT];
 #pragma unroll 1
         for (int I = 0; I < TILE_H / DPT; ++I) {
+            QVec<T> qc;
+            unsigned hm = 0;
 #pragma unroll
             for (int ii = 0; ii < DPT; ++ii) {
-                const T2 ra = rowA[ii];                                             // {df, dg} of row i + 1
-                const typename Tr<T>::RowBV rbn = Tr<T>::load_rowb(rowB + ii + 1);  // {inv, thr} of row i + 1
-                // next column entering this lane's window: x = i + 8*lane + 8 -> class ii, slot lane + I + 1;
-                // its cm8 is the threshold minimum over the CURRENT window [i + 8*lane, i + 8*lane + 8)
-                const T2 nd = colA[ii * COL_STRIDE];
-                const typename Tr<T>::ColV nb = Tr<T>::load_colb(colB + ii * COL_STRIDE);
-                T P[DPT];
+                if (ii % RB == 0) {
 #pragma unroll
-                for (int j = 0; j < DPT; ++j) P[j] = corr_of(qt[j], rb.inv, civ[(ii + j) & 7]);
-                const int thr = min(rb.thr, nb.cm8);
-                cdf[ii] = nd.x; cdg[ii] = nd.y; civ[ii] = nb.inv;
+                    for (int j = 0; j < DPT; ++j) qc.v[j] = qt[j];
+                    hm = 0;
+                }
+                // operands of sub-step ii + 1
+                const T2 ra_n = rowA[ii];
+                const T2 rb_n = rowB[ii];
+                const T2 nd_n = colA[((ii + 1) % DPT) * COL_STRIDE + (ii + 1) / DPT];
+                T2 cw_n[NWIN];
+#pragma unroll
+                for (int w = 0; w < NWIN; ++w) cw_n[w] = colW[((ii + 1 + FWIN * w) % DPT) * COL_STRIDE + (ii + 1 + FWIN * w) / DPT];
+                // filter on QT(row i)
+                bool pass = false;
+#pragma unroll
+                for (int w = 0; w < NWIN; ++w) {
+                    const int ka = key_of(mul_rn(rb.x, cw[w].x));
+                    const int kb = key_of(mul_rn(rb.y, cw[w].y));
+                    pass |= max_key8(qt + FWIN * w) > __vimin_s32_relu(ka, kb);
+                }
+                hm |= pass ? (1u << (ii % RB)) : 0u;
+                // QT(row i + 1)
+                cdf[ii] = nd.x; cdg[ii] = nd.y;
 #pragma unroll
                 for (int j = 0; j < DPT; ++j) {
-                    const int k = (ii + 1 + j) & 7;
-                    qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);     // QT(row i + 1)
+                    const int k = (ii + 1 + j) % DPT;
+                    qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);
                 }
-                const int m0 = __vimax3_s32(filter_key(P[0]), filter_key(P[1]), filter_key(P[2]));
-                const int m1 = __vimax3_s32(filter_key(P[3]), filter_key(P[4]), filter_key(P[5]));
-                const int m2 = __vimax3_s32(filter_key(P[6]), filter_key(P[7]), m0);
-                if (__builtin_expect(max(m1, m2) >= thr, 0))
-                    cold_row<T>(P[0], P[1], P[2], P[3], P[4], P[5], P[6], P[7], I * DPT + ii);
-                rb = rbn;
+                if (ii % RB == RB - 1) {
+                    if (__builtin_expect(__any_sync(FULL, hm != 0), 0)) {
+                        nhit += __reduce_add_sync(FULL, __popc(hm));
+                        hitcnt = replay_block<T, STRICT>(qc, hm, I * DPT + ii - (RB - 1), r0, c0, hitcnt, inv, prof, &nwin);
+                    }
+                }
+                ra = ra_n; rb = rb_n; nd = nd_n;
+#pragma unroll
+                for (int w = 0; w < NWIN; ++w) cw[w] = cw_n[w];
             }
-            rowA += DPT; rowB += DPT; colA += 1; colB += 1;
+            rowA += DPT; rowB += DPT; colA += 1; colW += 1;
         }
     }
-    flush_queue<T>();
-    if (lane == 0 && counter && S.ctx->slow) atomicAdd(counter, (unsigned long long)S.ctx->slow);
+    if (hitcnt > 0) nwin += drain_hits<T>(hitcnt, inv, prof);
+    if (counters) {
+        nwin = __reduce_add_sync(FULL, nwin);
+        if (lane == 0 && nhit) { atomicAdd(counters, (unsigned long long)nhit); atomicAdd(counters + 1, (unsigned long long)nwin); }
+    }
 }
 
 int band_count(int sublen, int excl) {
@@ -379,7 +450,7 @@ long long build_item_table(int sublen, int excl, int rank, int world, int seg_ro
 }
 
 // Default segment length: long enough that the re-seed (m FMAs per diagonal per segment against
-// 4 * seg_rows pipe operations) stays under ~2 %, short enough that a rank has several waves of items.
+// ~2.25 * seg_rows pipe operations) stays around 3 %, short enough that a rank has several waves of items.
 int default_seg_rows(int sublen, int excl, int m, int world, int sm_count) {
     int floor_rows = ((16 * m + 255) / 256) * 256;
     if (floor_rows < 1024) floor_rows = 1024;
@@ -391,24 +462,24 @@ int default_seg_rows(int sublen, int excl, int m, int world, int sm_count) {
 }
 
 template <typename T>
-static cudaError_t launch_tiles_t(const T *df_dg, const T *inv, const T *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *inv, const T *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
     if (p.seg_rows % TILE_H != 0 || p.seg_rows < 0) return cudaErrorInvalidValue;
-    const size_t smem = (size_t)(BAND_THREADS / 32) * WarpSmem<T>::BYTES;
+    const size_t smem = (size_t)cta_smem_bytes<T>();
     auto kern = p.strict ? tile_kernel<T, true> : tile_kernel<T, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), inv, qt0, p.series, p.mu, prof, p.item_start, p.nlb,
-                                                       p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.slow_counter);
+    kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), inv, qt0, p.series, p.mu,
+                                                       prof, p.item_start, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters);
     return cudaGetLastError();
 }
 
-cudaError_t launch_tiles_f64(const double *df_dg, const double *inv, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
-    return launch_tiles_t<double>(df_dg, inv, qt0, prof, p, s);
+cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *inv, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    return launch_tiles_t<double>(df_dg, nm, inv, qt0, prof, p, s);
 }
-cudaError_t launch_tiles_f32(const float *df_dg, const float *inv, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
-    return launch_tiles_t<float>(df_dg, inv, qt0, prof, p, s);
+cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *inv, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    return launch_tiles_t<float>(df_dg, nm, inv, qt0, prof, p, s);
 }
 
 }  // namespace mpb

@@ -22,7 +22,7 @@ F64, F32 = 0, 1
 FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED = 1, 2, 4
 _LIB = None
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # matrix-profile-hls_b200/
-LIB_PATH = os.path.join(_PKG_ROOT, "libmpb200.so")
+LIB_PATH = os.environ.get("MPB200_LIB") or os.path.join(_PKG_ROOT, "libmpb200.so")   # MPB200_LIB: tuning builds (csrc/Makefile VARIANT=)
 
 # record layouts: reference include/Config.hpp.in:43-73
 AGG_F64 = np.dtype([("value", "<f8"), ("index", "<i4"), ("_pad", "<i4")])
@@ -44,7 +44,7 @@ class MpbError(RuntimeError):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("precompute_ms", C.c_double), ("compute_ms", C.c_double), ("finalize_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("cells", C.c_int64), ("slow_updates", C.c_int64),
-                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32)]
+                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
