@@ -25,7 +25,7 @@ struct TileLaunch {
     int seg_rows;                       // rows per re-seeded segment (multiple of TILE_H); 0 = one full-length chain per diagonal
     bool strict;                        // un-fused QT update (the reference's rounding sequence)
     const double *series, *mu;          // T[n], mu[sublen] (re-seed operands)
-    const int *item_start;              // device: prefix table, nlb + 1 entries
+    const int *item_start;              // device: prefix table (nlb + 1 entries) followed by the band ids in visiting order (nlb entries)
     int nlb;                            // this rank's band count
     long long items;                    // total work items (= grid size)
     unsigned long long *counters;       // device: [0] thread-rows that passed the filter, [1] profile slots improved (may be null)

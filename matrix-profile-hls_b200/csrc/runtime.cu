@@ -319,7 +319,7 @@ static int plan_build_table(mpb_plan *p) {
     if (p->item_start) { cudaFree(p->item_start); p->item_start = nullptr; }
     CU(cudaMalloc((void **)&p->item_start, sizeof(int) * tab.size()));
     CU(cudaMemcpy(p->item_start, tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice));
-    p->nlb = (int)tab.size() - 1; p->items = items; p->seg_rows_eff = seg; p->table_dirty = false;
+    p->nlb = ((int)tab.size() - 1) / 2; p->items = items; p->seg_rows_eff = seg; p->table_dirty = false;
     return MPB_OK;
 }
 

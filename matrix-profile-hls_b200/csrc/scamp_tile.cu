@@ -30,14 +30,16 @@
 // passes.  The FP64 pipe therefore carries 2 DFMA per cell + 2 DMUL per 8 cells (2.25 pipe ops per cell
 // against the reference formulation's 4).
 //
-// Hits.  A thread-row that passes the filter parks its DPT QT values in a small per-warp hit buffer and the
-// warp goes straight back to the recurrence.  When enough hits wait (or the item ends) the warp drains the
-// buffer with all lanes in parallel: exact P = (QT * inv_r) * inv_c per cell (:84, the reference's rounding
-// order), exact compare against the live profile slot of the column and -- after a shuffle max over the
-// thread-row -- of the row, and a 128-bit compare-and-swap where it wins (mp_common.cuh: larger corr wins,
-// equal corr -> smaller index; deterministic for any arrival order or GPU count).  The profile (one 16-byte
-// {corr, index} slot per subsequence, row and column roles merged, HostSideComputation.hpp:61) lives in
-// HBM/L2 and is only ever touched by drains and by the per-tile threshold snapshots.
+// Hits.  The hot loop is branch-free in blocks of RB rows: it only records which (row, lane) pairs passed the
+// filter.  A block with a bit set is replayed from its starting QT values (same operations, same bits) and the
+// flagged thread-rows park their DPT QT values in a small per-warp hit buffer.  At the end of the tile (or
+// when the buffer fills) the warp drains the buffer with all lanes in parallel: each cell repeats the filter
+// on its own against the tile's per-column keys; survivors compute exact P = (QT * inv_r) * inv_c (:84, the
+// reference's rounding order) and apply it to the column's and the row's profile slot with a 128-bit
+// compare-and-swap (mp_common.cuh: larger corr wins, equal corr -> smaller index; deterministic for any
+// arrival order or GPU count).  The profile (one 16-byte {corr, index} slot per subsequence, row and column
+// roles merged, HostSideComputation.hpp:61) lives in HBM/L2 and is only ever touched by drains and by the
+// per-tile threshold snapshots.
 //
 // Staging.  Every WARP stages its own tile (TILE_H rows and the TILE_H + WARP_DIAGS columns they touch) in
 // its private slice of shared memory, synchronised with __syncwarp only -- there is no CTA-wide barrier in
@@ -107,6 +109,12 @@ __device__ __forceinline__ int key_of(double v) { return __double2hiint(v); }
 __device__ __forceinline__ int key_of(float v) { return __float_as_int(v); }
 __device__ __forceinline__ double slack(double) { return 1.0 - 1.0 / 262144.0; }
 __device__ __forceinline__ float slack(float) { return 1.0f - 1.0f / 262144.0f; }
+// +inf as a threshold means "never passes" and survives every product with a positive finite factor; the staged
+// terms are arranged so that inf never meets 0 (0 * inf is a NaN with the sign bit set, i.e. a key that always passes).
+__device__ __forceinline__ double pos_inf(double) { return __longlong_as_double(0x7ff0000000000000LL); }
+__device__ __forceinline__ float pos_inf(float) { return __int_as_float(0x7f800000); }
+__device__ __forceinline__ double tiny_best(double) { return 1e-300; }
+__device__ __forceinline__ float tiny_best(float) { return 1e-30f; }
 __device__ __forceinline__ void set_key(double &dst, int key) { dst = __hiloint2double(key, 0); }
 __device__ __forceinline__ void set_key(float &dst, int key) { dst = __int_as_float(key); }
 
@@ -127,11 +135,17 @@ extern __shared__ __align__(16) unsigned char smem_raw[];
 
 // ---------------------------------------------------------------------------------------------
 // Drain: applies the parked hits to the profile.  Lane e handles cell e of the buffer (hit e / DPT, diagonal
-// e % DPT), so 32 / DPT hits are resolved per pass with their memory round trips overlapped.  Warp-collective.
-// Returns the number of profile slots this warp actually improved (statistics only).
+// e % DPT), 32 / DPT hits per pass.  Hits never outlive the tile they were parked in, so every cell first
+// repeats the filter test on its own, against the tile's per-column key (exact up to the key's truncation)
+// and per-row terms in shared memory; only cells that survive touch the profile in HBM/L2:
+// exact P = (QT * inv_r) * inv_c (:84), 128-bit compare-and-swap on the column's and the row's slot
+// (mp_common.cuh), and the tile's own thresholds are raised with what came back.  Warp-collective.
+// Returns the number of profile slots this warp improved (statistics only).
 // ---------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __noinline__ unsigned drain_hits(int nhits, const T *__restrict__ inv, ProfileEntry *prof) {
+__device__ __noinline__ unsigned drain_hits(int nhits, int r0, int c0, const T *__restrict__ inv, const typename Tr<T>::T2 *__restrict__ nm,
+                                            ProfileEntry *prof) {
+    using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
     __syncwarp();
@@ -139,29 +153,30 @@ __device__ __noinline__ unsigned drain_hits(int nhits, const T *__restrict__ inv
     const int ncell = nhits * DPT;
     for (int base = 0; base < ncell; base += 32) {
         const int e = base + lane;
-        const bool act = e < ncell;
-        const int h = act ? e / DPT : 0, j = e % DPT;
-        const int2 mt = S.hitM[h];
-        const T q = S.hitQ[h * DPT + j];
-        const int row = mt.x, col = mt.y + j;
-        const T p = corr_of(q, inv[row], inv[col]);
-        double pv = act ? (double)p : -1.0;
-        if (!(pv > 0.0)) pv = -1.0;                          // P <= 0 and NaN never enter the profile (it starts at +0.0)
-        if (pv > 0.0) {
-            const double before = profile_update(prof + col, pv, row);
-            wins += before == pv;
-        }
-        double bv = pv;
-        int bc = col;
-#pragma unroll
-        for (int s = 1; s < DPT; s <<= 1) {                  // best of the thread-row; ties keep the smaller column
-            const double ov = __shfl_xor_sync(FULL, bv, s);
-            const int oc = __shfl_xor_sync(FULL, bc, s);
-            if (ov > bv || (ov == bv && oc < bc)) { bv = ov; bc = oc; }
-        }
-        if (act && j == 0 && bv > 0.0) {
-            const double before = profile_update(prof + row, bv, bc);
-            wins += before == bv;
+        if (e < ncell) {
+            const int h = e / DPT, j = e % DPT;
+            const int2 mt = S.hitM[h];
+            const T q = S.hitQ[h * DPT + j];
+            const int row = mt.x, col = mt.y + j;
+            const int i = row - r0, p = col_slot(col - c0);
+            const T2 rb = S.rowB[i];
+            T cq;
+            set_key(cq, S.ck[p]);
+            const int ka = key_of(mul_rn(rb.x, S.colW[p].x));        // row side: best_r*norm_r * (min norm over [col, col+FWIN) <= norm_c)
+            const int kb = key_of(mul_rn(rb.y, cq));                 // column side: norm_r * best_c*norm_c
+            if (key_of(q) > __vimin_s32_relu(ka, kb)) {
+                const T ic = inv[col];
+                const double pv = (double)corr_of(q, inv[row], ic);
+                if (pv > 0.0) {                                      // P <= 0 and NaN never enter the profile (it starts at +0.0)
+                    const T norm_c = nm[col].x;
+                    const double after_c = profile_update(prof + col, pv, row);
+                    const double after_r = profile_update(prof + row, pv, col);
+                    wins += (after_c == pv) + (after_r == pv);
+                    atomicMax(&S.ck[p], key_of(mul_rn((T)after_c, norm_c)));
+                    const T rq = mul_rn((T)after_r, rb.y);
+                    if (rq > rb.x) S.rowB[i].x = rq;                 // racing lanes may lose an update: thresholds only get looser
+                }
+            }
         }
     }
     __syncwarp();
@@ -178,7 +193,7 @@ template <typename T> struct QVec { T v[DPT]; };
 
 template <typename T, bool STRICT>
 __device__ __noinline__ int replay_block(QVec<T> qc, unsigned hm, int i0, int r0, int c0, int hitcnt, const T *__restrict__ inv,
-                                         ProfileEntry *prof, unsigned *wins) {
+                                         const typename Tr<T>::T2 *__restrict__ nm, ProfileEntry *prof, unsigned *wins) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
@@ -196,7 +211,7 @@ __device__ __noinline__ int replay_block(QVec<T> qc, unsigned hm, int i0, int r0
                 S.hitM[pos] = make_int2(r0 + i, c0 + i + DPT * lane);
             }
             hitcnt += __popc(mk);
-            if (hitcnt > HDRAIN) { *wins += drain_hits<T>(hitcnt, inv, prof); hitcnt = 0; }
+            if (hitcnt > HDRAIN) { *wins += drain_hits<T>(hitcnt, r0, c0, inv, nm, prof); hitcnt = 0; }
         }
         if (t < last) {
             const T2 ra = S.rowA[i + 1];
@@ -283,7 +298,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
     const int item = blockIdx.x;
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
     const int seg = item - item_start[lo];
-    const int band = rank + lo * world;
+    const int band = item_start[nlb + 1 + lo];                  // band ids follow the prefix table
     const int d0w = excl + band * BAND_W + warp * WARP_DIAGS;   // first (longest) diagonal of this warp
     const int nrows = sublen - d0w;                             // rows of that diagonal
     const int rbeg = seg_rows > 0 ? seg * seg_rows : 0;
@@ -312,8 +327,8 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 #pragma unroll
         for (int i = lane; i < ROWS_STAGED; i += 32) {
             S.rowA[i] = df_dg[r0 + i];
-            const T norm = nm[r0 + i].x;
-            const T best = (T)__ldcg(&prof[r0 + i].corr);
+            const T norm = nm[r0 + i].x;                        // +inf on the padding
+            const T best = max((T)__ldcg(&prof[r0 + i].corr), tiny_best(T(0)));   // never 0: 0 * inf would be a NaN
             T2 rb;
             rb.y = mul_rn(norm, sl);
             rb.x = mul_rn(best, rb.y);
@@ -329,7 +344,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             w.x = nv.y;
             w.y = T(0);
             S.colW[p] = w;
-            S.ck[p] = key_of(mul_rn(best, nv.x));
+            S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn(best, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
         }
         __syncwarp();
         // window minima of the column keys: lane owns entry q (columns DPT*q .. DPT*q + DPT - 1) and needs entry q + 1
@@ -338,7 +353,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 #pragma unroll
             for (int k = 0; k < DPT; ++k) a[k] = S.ck[k * COL_STRIDE + q];
 #pragma unroll
-            for (int k = 0; k < FWIN; ++k) a[DPT + k] = q + 1 < COL_STRIDE ? S.ck[k * COL_STRIDE + q + 1] : 0x7fffffff;
+            for (int k = 0; k < FWIN; ++k) a[DPT + k] = q + 1 < COL_STRIDE ? S.ck[k * COL_STRIDE + q + 1] : key_of(pos_inf(T(0)));
 #pragma unroll
             for (int k = 0; k < DPT; ++k) {
                 int mn = a[k];
@@ -410,7 +425,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
                 if (ii % RB == RB - 1) {
                     if (__builtin_expect(__any_sync(FULL, hm != 0), 0)) {
                         nhit += __reduce_add_sync(FULL, __popc(hm));
-                        hitcnt = replay_block<T, STRICT>(qc, hm, I * DPT + ii - (RB - 1), r0, c0, hitcnt, inv, prof, &nwin);
+                        hitcnt = replay_block<T, STRICT>(qc, hm, I * DPT + ii - (RB - 1), r0, c0, hitcnt, inv, nm, prof, &nwin);
                     }
                 }
                 ra = ra_n; rb = rb_n; nd = nd_n;
@@ -419,8 +434,8 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             }
             rowA += DPT; rowB += DPT; colA += 1; colW += 1;
         }
+        if (hitcnt > 0) { nwin += drain_hits<T>(hitcnt, r0, c0, inv, nm, prof); hitcnt = 0; }   // hits never outlive their tile
     }
-    if (hitcnt > 0) nwin += drain_hits<T>(hitcnt, inv, prof);
     if (counters) {
         nwin = __reduce_add_sync(FULL, nwin);
         if (lane == 0 && nhit) { atomicAdd(counters, (unsigned long long)nhit); atomicAdd(counters + 1, (unsigned long long)nwin); }
@@ -432,17 +447,20 @@ int band_count(int sublen, int excl) {
     return ndiag <= 0 ? 0 : (ndiag + BAND_W - 1) / BAND_W;
 }
 
-// Prefix table of work items for the bands of `rank`: band b = rank + lb * world owns
-// ceil(rows(b) / seg_rows) items (one when seg_rows == 0). Returns the total item count.
+// Work-item table of `rank`, whose bands are b = rank, rank + world, ...: entries [0, nlb] are the prefix sums of
+// the items per band (ceil(rows(b) / seg_rows), one when seg_rows == 0) and entries [nlb + 1, 2 nlb] the band ids
+// in visiting order (increasing lag: measured better than a bit-reversed order, which delays the first visit of
+// many rows and triples the filter hits at n = 2^18).  Returns the total item count.
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start) {
     const int nb = band_count(sublen, excl);
     const int nlb = nb > rank ? (nb - rank + world - 1) / world : 0;
-    item_start.assign((size_t)nlb + 1, 0);
+    item_start.assign(2 * (size_t)nlb + 1, 0);
     long long total = 0;
     for (int lb = 0; lb < nlb; ++lb) {
         const int band = rank + lb * world;
         const int nrows = sublen - (excl + band * BAND_W);
         item_start[lb] = (int)total;
+        item_start[(size_t)nlb + 1 + lb] = band;
         total += seg_rows > 0 ? (nrows + seg_rows - 1) / seg_rows : 1;
     }
     item_start[nlb] = (int)total;
