@@ -98,7 +98,8 @@ typedef struct {
     int32_t bands;        /* diagonal bands this rank walked */
     int32_t items;        /* (band, row segment) work items = CTAs of the tile kernel */
     int32_t segment_rows; /* rows per re-seeded segment (0 = full-length chains) */
-    int64_t filter_hits;  /* thread-rows (DPT cells each) that passed the QT-domain filter and were checked exactly */
+    int64_t filter_hits;  /* cells that passed the QT-domain filter and were checked exactly against the profile */
+    int64_t replays;      /* 8-row x 8-diagonal x 32-lane blocks walked a second time because a cell in them passed the block filter */
 } mpb_timings;
 
 /* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised

@@ -36,8 +36,10 @@ static_assert(sizeof(Aggregate<float>) == 8 && sizeof(InputDataPack<float>) == 1
 #define MPB_WARPS 4
 #endif
 constexpr int DPT = MPB_DPT;              // diagonals per thread (register micro-tile width): 8 or 16
-constexpr int FWIN = 8;                   // columns per filter window (one threshold test covers FWIN cells)
-constexpr int NWIN = DPT / FWIN;          // filter windows per thread-row
+constexpr int FWIN = 8;                   // columns a lane covers in one row
+constexpr int NWIN = DPT / FWIN;
+constexpr int RB = 8;                     // rows per branch-free block of the hot loop (one filter test per block and lane)
+constexpr int MNC_WIN = FWIN + RB - 1;    // columns a lane covers in one block = width of the staged column-window minima
 constexpr int BAND_WARPS = MPB_WARPS;     // warps per CTA
 constexpr int BAND_THREADS = 32 * BAND_WARPS;
 constexpr int WARP_DIAGS = DPT * 32;      // diagonals per warp

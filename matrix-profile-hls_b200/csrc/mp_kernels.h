@@ -12,9 +12,9 @@ cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream
 cudaError_t launch_mu_window(const double *T, int n, int m, double *mu, cudaStream_t s);    // exact window means (parallel)
 cudaError_t launch_stats_f64(const double *T, const double *mu, int n, int m, double *df_dg, double *inv, double *qt0, cudaStream_t s);
 cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, float *df_dg, float *inv, float *qt0, cudaStream_t s);
-// nm[i] = {norm_i = 1 / inv_i, min of norm over [i, i + FWIN)} for i < np; +inf on the padding (inv = 0)
-cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, cudaStream_t s);
-cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, cudaStream_t s);
+// nm[i] = {norm_i = 1 / inv_i, inv_i}, mnc[i] = min of norm over [i, i + MNC_WIN), for i < np; norm = +inf on the padding (inv = 0)
+cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, double *mnc, cudaStream_t s);
+cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, float *mnc, cudaStream_t s);
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s);
 cudaError_t launch_pack_input_f64(const double *df_dg, const double *inv, const double *qt0, int sublen, void *out, cudaStream_t s);
 cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const float *qt0, int sublen, void *out, cudaStream_t s);
@@ -28,13 +28,13 @@ struct TileLaunch {
     const int *item_start;              // device: prefix table (nlb + 1 entries) followed by the band ids in visiting order (nlb entries)
     int nlb;                            // this rank's band count
     long long items;                    // total work items (= grid size)
-    unsigned long long *counters;       // device: [0] thread-rows that passed the filter, [1] profile slots improved (may be null)
+    unsigned long long *counters;       // device: [0] cells parked, [1] profile slots improved, [2] blocks replayed (may be null)
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);
 int default_seg_rows(int sublen, int excl, int m, int world, int sm_count);
-cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *inv, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
-cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *inv, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *mnc, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *mnc, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 
 // kernel (3): merge.cu
 cudaError_t launch_finalize(const ProfileEntry *prof, int sublen, int m, double *MP, int32_t *MPI, double *corr, cudaStream_t s);

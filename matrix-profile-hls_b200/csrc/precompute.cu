@@ -144,23 +144,24 @@ stats_kernel(const double *__restrict__ T, const double *__restrict__ mu, int n,
     qt0[i] = (OutT)qt;
 }
 
-// Threshold operands of the tile kernel: norm_i = 1 / inv_i and its minimum over the filter window that starts
-// at i.  Beyond sublen inv is the zero padding, so norm = +inf there ("never a candidate").
+// Threshold operands of the tile kernel: {norm_i = 1 / inv_i, inv_i} pairs, and the minimum of norm over the MNC_WIN
+// columns that start at i (the columns one lane covers in one block of the hot loop).  Beyond sublen inv is the zero padding, so norm = +inf there ("never a candidate").
 template <typename OutT>
-__global__ void norm_kernel(const OutT *__restrict__ inv, int sublen, int np, OutT *__restrict__ nm) {
+__global__ void norm_kernel(const OutT *__restrict__ inv, int sublen, int np, OutT *__restrict__ nm, OutT *__restrict__ mnc) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= np) return;
     const OutT inf = (OutT)__longlong_as_double(0x7ff0000000000000LL);
     OutT first = inf, mn = inf;
 #pragma unroll
-    for (int k = 0; k < FWIN; ++k) {
+    for (int k = 0; k < MNC_WIN; ++k) {
         const int c = i + k;
         const OutT v = c < sublen ? (OutT)1 / inv[c] : inf;
         if (k == 0) first = v;
         mn = v < mn ? v : mn;
     }
     nm[2 * (size_t)i] = first;
-    nm[2 * (size_t)i + 1] = mn;
+    nm[2 * (size_t)i + 1] = i < sublen ? inv[i] : (OutT)0;
+    mnc[i] = mn;
 }
 
 __global__ void profile_init_kernel(ProfileEntry *prof, int count) {
@@ -209,12 +210,12 @@ cudaError_t launch_stats_f64(const double *T, const double *mu, int n, int m, do
 cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, float *df_dg, float *inv, float *qt0, cudaStream_t s) {
     return launch_stats_t<float>(T, mu, n, m, df_dg, inv, qt0, s);
 }
-cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, cudaStream_t s) {
-    norm_kernel<double><<<(np + 255) / 256, 256, 0, s>>>(inv, sublen, np, nm);
+cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, double *mnc, cudaStream_t s) {
+    norm_kernel<double><<<(np + 255) / 256, 256, 0, s>>>(inv, sublen, np, nm, mnc);
     return cudaGetLastError();
 }
-cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, cudaStream_t s) {
-    norm_kernel<float><<<(np + 255) / 256, 256, 0, s>>>(inv, sublen, np, nm);
+cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, float *mnc, cudaStream_t s) {
+    norm_kernel<float><<<(np + 255) / 256, 256, 0, s>>>(inv, sublen, np, nm, mnc);
     return cudaGetLastError();
 }
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s) {

@@ -56,7 +56,7 @@ struct mpb_plan {
     int rank = 0, world = 1;
     double *T = nullptr, *mu = nullptr;
     void *df_dg = nullptr, *inv = nullptr, *qt0 = nullptr;    // data_t arrays, zero-padded to np
-    void *nm = nullptr;                                       // data_t {norm, window-min norm} pairs, np entries
+    void *nm = nullptr, *mnc = nullptr;                       // data_t {norm, inv} pairs and window-min norms, np entries
     mpb::ProfileEntry *prof = nullptr;                        // np slots
     double *MP = nullptr, *corr = nullptr;
     int32_t *MPI = nullptr;
@@ -243,7 +243,7 @@ int mpb_plan_destroy(mpb_plan *p) {
     if (!p) return MPB_OK;
     cudaSetDevice(p->ctx->device);
     cudaStreamSynchronize(p->ctx->stream);
-    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start};
+    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start};
     for (void *q : ptrs) if (q) cudaFree(q);
     for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
     delete p;
@@ -274,17 +274,18 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     ALLOC(p->inv, es * np);
     ALLOC(p->qt0, es * np);
     ALLOC(p->nm, 2 * es * np);
+    ALLOC(p->mnc, es * np);
     ALLOC(p->prof, sizeof(mpb::ProfileEntry) * np);
     ALLOC(p->MP, sizeof(double) * (size_t)p->sublen);
     ALLOC(p->corr, sizeof(double) * (size_t)p->sublen);
     ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
-    ALLOC(p->slow_counter, 2 * sizeof(unsigned long long));
+    ALLOC(p->slow_counter, 4 * sizeof(unsigned long long));
 #undef ALLOC
     // zero padding beyond sublen is what lets tiles run off the matrix edge without bounds checks
     CU(cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream));
     CU(cudaMemsetAsync(p->inv, 0, es * np, c->stream));
     CU(cudaMemsetAsync(p->qt0, 0, es * np, c->stream));
-    CU(cudaMemsetAsync(p->slow_counter, 0, 2 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), c->stream));
     for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
     p->tm.cells = mpb_useful_cells(n, m);
     *out = p;
@@ -346,8 +347,8 @@ int mpb_plan_precompute(mpb_plan *p) {
     else CU(mpb::launch_mu_window(p->T, p->n, p->m, p->mu, s));
     if (p->dtype == MPB_F64) CU(mpb::launch_stats_f64(p->T, p->mu, p->n, p->m, (double *)p->df_dg, (double *)p->inv, (double *)p->qt0, s));
     else CU(mpb::launch_stats_f32(p->T, p->mu, p->n, p->m, (float *)p->df_dg, (float *)p->inv, (float *)p->qt0, s));
-    if (p->dtype == MPB_F64) CU(mpb::launch_norm_f64((const double *)p->inv, p->sublen, p->np, (double *)p->nm, s));
-    else CU(mpb::launch_norm_f32((const float *)p->inv, p->sublen, p->np, (float *)p->nm, s));
+    if (p->dtype == MPB_F64) CU(mpb::launch_norm_f64((const double *)p->inv, p->sublen, p->np, (double *)p->nm, (double *)p->mnc, s));
+    else CU(mpb::launch_norm_f32((const float *)p->inv, p->sublen, p->np, (float *)p->nm, (float *)p->mnc, s));
     CU(mpb::launch_profile_init(p->prof, p->np, s));
     CU(cudaEventRecord(p->ev[3], s));
     p->tm.launches = 4;
@@ -367,10 +368,10 @@ int mpb_plan_compute(mpb_plan *p) {
     tl.series = p->T; tl.mu = p->mu;
     tl.item_start = p->item_start; tl.nlb = p->nlb; tl.items = p->items;
     tl.counters = p->slow_counter;
-    CU(cudaMemsetAsync(p->slow_counter, 0, 2 * sizeof(unsigned long long), s));
+    CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
     CU(cudaEventRecord(p->ev[4], s));
-    if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->inv, (const double *)p->qt0, p->prof, tl, s));
-    else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->inv, (const float *)p->qt0, p->prof, tl, s));
+    if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->mnc, (const double *)p->qt0, p->prof, tl, s));
+    else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->mnc, (const float *)p->qt0, p->prof, tl, s));
     CU(cudaEventRecord(p->ev[5], s));
     p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
     p->tm.launches += p->items > 0 ? 1 : 0;
@@ -483,10 +484,11 @@ int mpb_plan_timings(mpb_plan *p, mpb_timings *out) {
     t.finalize_ms = span(5, 6);
     t.d2h_ms = span(6, 7);
     t.total_ms = span(p->ran_h2d ? 0 : 2, 7);
-    unsigned long long cnt[2] = {0, 0};
+    unsigned long long cnt[4] = {0, 0, 0, 0};
     CU(cudaMemcpy(cnt, p->slow_counter, sizeof cnt, cudaMemcpyDeviceToHost));
     t.filter_hits = (int64_t)cnt[0];
     t.slow_updates = (int64_t)cnt[1];
+    t.replays = (int64_t)cnt[2];
     *out = t;
     return MPB_OK;
 }

@@ -20,26 +20,26 @@
 // cell) and compares it with the row and column aggregates (:87-96).  Here the comparison is moved to the QT
 // domain: a cell can only improve row r or column c if
 //     QT >= norm_r * norm_c * min(best_r, best_c),        norm = 1 / inv,
-// and for the FWIN = 8 cells a lane holds in one row (8 adjacent columns) that is implied by
-//     QT >= min( (best_r * norm_r) * min_c norm_c ,  norm_r * min_c (best_c * norm_c) )   =: theta(r, window)
-// -- two multiplies per 8 cells instead of two per cell.  Row terms {best_r*norm_r, norm_r} and the window
-// minima {min norm_c, min best_c*norm_c} are staged per tile; the test itself compares the HIGH 32 BITS of
-// max(QT_0..7) and theta as integers (VIMNMX3 tree + ISETP on the ALU pipe; an fp64 compare would be a
-// DSETP on the FP64 pipe).  The staged row terms are scaled by (1 - 2^-18), which more than covers every
-// rounding on the way, so the filter has no false negatives: every cell that beats the current profile
-// passes.  The FP64 pipe therefore carries 2 DFMA per cell + 2 DMUL per 8 cells (2.25 pipe ops per cell
-// against the reference formulation's 4).
+// and for a BLOCK of cells -- the DPT = 8 diagonals of a lane over RB = 8 consecutive rows, i.e. rows
+// [i0, i0 + 8) x columns [y, y + 15) -- that is implied by
+//     QT >= min( min_r(best_r * norm_r) * min_c norm_c ,  min_r norm_r * min_c (best_c * norm_c) )   =: theta
+// with the minima taken over the block's rows and its 15-column window.  The hot loop therefore only keeps a
+// running maximum of the HIGH 32 BITS of its QT values (VIMNMX3 on the ALU pipe: 4 per 8 cells; an fp64
+// compare would be a DSETP on the FP64 pipe) and tests it ONCE per block against theta (2 DMUL per 64 cells).
+// Row-block minima and column-window minima are staged per tile; the row terms are scaled by (1 - 2^-18),
+// which more than covers every rounding on the way, so the filter has no false negatives: every cell that
+// beats the current profile makes its block pass.  The FP64 pipe carries 2 DFMA per cell + 2 DMUL per 64
+// cells (2.03 pipe ops per cell against the reference formulation's 4).
 //
-// Hits.  The hot loop is branch-free in blocks of RB rows: it only records which (row, lane) pairs passed the
-// filter.  A block with a bit set is replayed from its starting QT values (same operations, same bits) and the
-// flagged thread-rows park their DPT QT values in a small per-warp hit buffer.  At the end of the tile (or
-// when the buffer fills) the warp drains the buffer with all lanes in parallel: each cell repeats the filter
-// on its own against the tile's per-column keys; survivors compute exact P = (QT * inv_r) * inv_c (:84, the
-// reference's rounding order) and apply it to the column's and the row's profile slot with a 128-bit
-// compare-and-swap (mp_common.cuh: larger corr wins, equal corr -> smaller index; deterministic for any
-// arrival order or GPU count).  The profile (one 16-byte {corr, index} slot per subsequence, row and column
-// roles merged, HostSideComputation.hpp:61) lives in HBM/L2 and is only ever touched by drains and by the
-// per-tile threshold snapshots.
+// Hits.  A block that passes is replayed from its starting QT values (same operations, same bits), this time
+// with the per-row form of the test; the thread-rows that pass it park their 8 QT values in a small per-warp
+// hit buffer.  At the end of the tile (or when the buffer fills) the warp drains the buffer with all lanes in
+// parallel: each cell repeats the test on its own against the tile's per-column keys; survivors compute exact
+// P = (QT * inv_r) * inv_c (:84, the reference's rounding order) and apply it to the column's and the row's
+// profile slot with a 128-bit compare-and-swap (mp_common.cuh: larger corr wins, equal corr -> smaller index;
+// deterministic for any arrival order or GPU count).  The profile (one 16-byte {corr, index} slot per
+// subsequence, row and column roles merged, HostSideComputation.hpp:61) lives in HBM/L2 and is only ever
+// touched by drains and by the per-tile threshold snapshots.
 //
 // Staging.  Every WARP stages its own tile (TILE_H rows and the TILE_H + WARP_DIAGS columns they touch) in
 // its private slice of shared memory, synchronised with __syncwarp only -- there is no CTA-wide barrier in
@@ -54,43 +54,51 @@ template <typename T> struct Tr;
 template <> struct Tr<double> { using T2 = double2; };
 template <> struct Tr<float> { using T2 = float2; };
 
-#ifndef MPB_RB
-#define MPB_RB 8
-#endif
-constexpr int RB = MPB_RB;                // rows per branch-free block of the hot loop (one vote + branch per block)
-static_assert(DPT % RB == 0, "RB");
-constexpr int HCAP = 48;                  // hit buffer capacity (thread-rows)
-constexpr int HDRAIN = HCAP - 32;         // drain once more than this many hits wait (a row can add up to 32)
+static_assert(DPT == 8 && RB == DPT && NWIN == 1, "this kernel version: 8 diagonals per lane, blocks of 8 rows");
+constexpr int HCAP = 48;                  // hit buffer capacity (thread-rows of DPT cells)
+constexpr int HDRAIN = HCAP - 32;         // drain once more than this many thread-rows wait (a row can add up to 32)
 constexpr int SEED_KC = TILE_H;           // k-chunk of the seed dot products (series samples staged per pass)
 constexpr int ROWS_STAGED = TILE_H + 8;   // TILE_H rows + the first row of the next tile (pipelined QT step) + prefetch slack
+constexpr int ROW_BLOCKS = ROWS_STAGED / RB;
 constexpr int COL_SLOTS = DPT * COL_STRIDE;
 constexpr unsigned FULL = 0xffffffffu;
 
 template <typename T>
 struct WarpSmem {
     using T2 = typename Tr<T>::T2;
-    static constexpr int BYTES = 2 * ROWS_STAGED * (int)sizeof(T2) + 2 * COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * 4 +
-                                 HCAP * DPT * (int)sizeof(T) + HCAP * 8;
-    T2 *rowA;     // [i] = {df_r, dg_r}
-    T2 *rowB;     // [i] = {best_r * norm_r * s, norm_r * s},  s = 1 - 2^-18
-    T2 *colA;     // [slot(x)] = {df_c, dg_c}
-    T2 *colW;     // [slot(y)] = {min norm_c, min best_c * norm_c} over the window of FWIN columns starting at y
-    int *ck;      // [slot(x)] = filter key of best_c * norm_c (input of the window minimum)
-    T *hitQ;      // [h][DPT] parked QT values
-    int2 *hitM;   // [h] = {row, first column}
+    static constexpr int NK = (COL_STRIDE + 3) / 4 * 4;
+    static constexpr int BYTES = 2 * ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + 2 * COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * 4 + COL_SLOTS * 8 +
+                                 HCAP * DPT * (int)sizeof(T) + HCAP * 8 + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + NK * (int)sizeof(T) + 16;
+    T2 *rowA;         // [i] = {df_r, dg_r}
+    T2 *rowB;         // [i] = {best_r * norm_r * s, norm_r * s},  s = 1 - 2^-18  (tile-start snapshot)
+    double2 *rowC;    // [i] = {best correlation of the row as this warp knows it, inv_r}
+    T2 *colA;         // [slot(x)] = {df_c, dg_c}
+    T2 *colW;         // [slot(y)] = {inv_y, min best_c * norm_c over the MNC_WIN columns starting at y (snapshot)}
+    int *ck;          // [slot(x)] = filter key of best_c * norm_c (input of the window minimum)
+    double *colBest;  // [slot(x)] = best correlation of the column as this warp knows it
+    T *hitQ;          // [h][DPT] QT values of a parked thread-row
+    int2 *hitM;       // [h] = {tile row i, window column x of its first cell}
+    T2 *rowK;         // [b] = minima of rowB over the rows [RB*b, RB*b + RB)
+    T *mncK;          // [q] = min of norm over the MNC_WIN columns starting at window column DPT*q
+    unsigned *stat;   // [0] candidates parked, [1] profile slots improved, [2] blocks replayed
     __device__ __forceinline__ explicit WarpSmem(unsigned char *base) {
         rowA = reinterpret_cast<T2 *>(base);
         rowB = rowA + ROWS_STAGED;
-        colA = rowB + ROWS_STAGED;
+        rowC = reinterpret_cast<double2 *>(rowB + ROWS_STAGED);
+        colA = reinterpret_cast<T2 *>(rowC + ROWS_STAGED);
         colW = colA + COL_SLOTS;
         ck = reinterpret_cast<int *>(colW + COL_SLOTS);
-        hitQ = reinterpret_cast<T *>(ck + COL_SLOTS);
+        colBest = reinterpret_cast<double *>(ck + COL_SLOTS);
+        hitQ = reinterpret_cast<T *>(colBest + COL_SLOTS);
         hitM = reinterpret_cast<int2 *>(hitQ + HCAP * DPT);
+        rowK = reinterpret_cast<T2 *>(hitM + HCAP);
+        mncK = reinterpret_cast<T *>(rowK + (ROW_BLOCKS + 1) / 2 * 2);
+        stat = reinterpret_cast<unsigned *>(mncK + NK);
     }
 };
 static_assert(WarpSmem<double>::BYTES % 16 == 0 && WarpSmem<float>::BYTES % 16 == 0, "warp slices stay 16-byte aligned");
 static_assert((ROWS_STAGED * sizeof(float2)) % 16 == 0 && (COL_SLOTS * sizeof(float2)) % 16 == 0 && (COL_SLOTS * 4) % 16 == 0 &&
-              (HCAP * DPT * sizeof(float)) % 16 == 0, "sub-arrays stay 16-byte aligned");
+              (COL_SLOTS * 8) % 16 == 0, "sub-arrays stay 16-byte aligned");
 static_assert(2 * ROWS_STAGED * sizeof(float2) >= SEED_KC * sizeof(double), "seed operand A aliases rowA/rowB");
 static_assert(2 * COL_SLOTS * sizeof(float2) >= COL_SLOTS * sizeof(double), "seed window U aliases colA/colW");
 static_assert(SEED_KC + WARP_DIAGS + DPT <= COL_WIN && SEED_KC % DPT == 0, "seed window fits the column slots");
@@ -103,8 +111,7 @@ template <typename T> constexpr int ctas_per_sm() {
 __device__ __forceinline__ int col_slot(int x) { return (x % DPT) * COL_STRIDE + (x / DPT); }
 
 // Filter key: the high word of the IEEE pattern, monotone for positive values; negative values have the sign
-// bit set (negative as an int) and never pass; NaN (e.g. 0 * inf on zero padding) is a huge positive key,
-// which as a threshold means "never passes".
+// bit set (negative as an int) and never pass.
 __device__ __forceinline__ int key_of(double v) { return __double2hiint(v); }
 __device__ __forceinline__ int key_of(float v) { return __float_as_int(v); }
 __device__ __forceinline__ double slack(double) { return 1.0 - 1.0 / 262144.0; }
@@ -133,93 +140,163 @@ __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, 
 
 extern __shared__ __align__(16) unsigned char smem_raw[];
 
+// 64-bit max on a shared-memory double that is known to be >= +0.0 (positive IEEE patterns order like integers)
+__device__ __forceinline__ double smem_max_pos(double *addr, double v) {
+    return __longlong_as_double((long long)atomicMax(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)__double_as_longlong(v)));
+}
+
 // ---------------------------------------------------------------------------------------------
-// Drain: applies the parked hits to the profile.  Lane e handles cell e of the buffer (hit e / DPT, diagonal
-// e % DPT), 32 / DPT hits per pass.  Hits never outlive the tile they were parked in, so every cell first
-// repeats the filter test on its own, against the tile's per-column key (exact up to the key's truncation)
-// and per-row terms in shared memory; only cells that survive touch the profile in HBM/L2:
-// exact P = (QT * inv_r) * inv_c (:84), 128-bit compare-and-swap on the column's and the row's slot
-// (mp_common.cuh), and the tile's own thresholds are raised with what came back.  Warp-collective.
-// Returns the number of profile slots this warp improved (statistics only).
+// Drain: resolves the parked thread-rows, one CELL per lane (hit e / DPT, diagonal e % DPT), 32 / DPT thread-rows
+// per pass.  Everything a cell needs is in the tile's shared memory: exact P = (QT * inv_r) * inv_c (:84, the
+// reference's rounding order) is compared with the warp's own view of the column's best (atomic max, so of the
+// cells that compete for a column in one pass only improvements survive) and -- after a shuffle max over the
+// thread-row -- of the row's best.  Only cells that improve that view touch the profile in HBM/L2, with a 128-bit
+// compare-and-swap (mp_common.cuh: larger corr wins, equal corr -> smaller index).  Warp-collective.
 // ---------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __noinline__ unsigned drain_hits(int nhits, int r0, int c0, const T *__restrict__ inv, const typename Tr<T>::T2 *__restrict__ nm,
-                                            ProfileEntry *prof) {
-    using T2 = typename Tr<T>::T2;
+__device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry *prof) {
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
     __syncwarp();
     unsigned wins = 0;
     const int ncell = nhits * DPT;
+#pragma unroll 1
     for (int base = 0; base < ncell; base += 32) {
         const int e = base + lane;
-        if (e < ncell) {
-            const int h = e / DPT, j = e % DPT;
-            const int2 mt = S.hitM[h];
-            const T q = S.hitQ[h * DPT + j];
-            const int row = mt.x, col = mt.y + j;
-            const int i = row - r0, p = col_slot(col - c0);
-            const T2 rb = S.rowB[i];
-            T cq;
-            set_key(cq, S.ck[p]);
-            const int ka = key_of(mul_rn(rb.x, S.colW[p].x));        // row side: best_r*norm_r * (min norm over [col, col+FWIN) <= norm_c)
-            const int kb = key_of(mul_rn(rb.y, cq));                 // column side: norm_r * best_c*norm_c
-            if (key_of(q) > __vimin_s32_relu(ka, kb)) {
-                const T ic = inv[col];
-                const double pv = (double)corr_of(q, inv[row], ic);
-                if (pv > 0.0) {                                      // P <= 0 and NaN never enter the profile (it starts at +0.0)
-                    const T norm_c = nm[col].x;
-                    const double after_c = profile_update(prof + col, pv, row);
-                    const double after_r = profile_update(prof + row, pv, col);
-                    wins += (after_c == pv) + (after_r == pv);
-                    atomicMax(&S.ck[p], key_of(mul_rn((T)after_c, norm_c)));
-                    const T rq = mul_rn((T)after_r, rb.y);
-                    if (rq > rb.x) S.rowB[i].x = rq;                 // racing lanes may lose an update: thresholds only get looser
-                }
-            }
+        const bool act = e < ncell;
+        const int h = act ? e / DPT : 0, j = e % DPT;
+        const int2 mt = S.hitM[h];
+        const int i = mt.x, x = mt.y + j;
+        const int p = col_slot(x);
+        const double2 rc = S.rowC[i];
+        double pv = (double)corr_of(S.hitQ[h * DPT + j], (T)rc.y, S.colW[p].x);
+        if (!act || !(pv > 0.0)) pv = -1.0;                  // P <= 0 and NaN never enter the profile (it starts at +0.0)
+        if (pv > 0.0 && pv >= S.colBest[p]) {
+            if (pv >= smem_max_pos(&S.colBest[p], pv)) wins += profile_update(prof + c0 + x, pv, r0 + i) == pv;
+        }
+        double bv = pv;                                      // best of the thread-row; ties keep the smaller column
+        int bx = x;
+#pragma unroll
+        for (int sft = 1; sft < DPT; sft <<= 1) {
+            const double ov = __shfl_xor_sync(FULL, bv, sft);
+            const int ox = __shfl_xor_sync(FULL, bx, sft);
+            if (ov > bv || (ov == bv && ox < bx)) { bv = ov; bx = ox; }
+        }
+        if (j == 0 && bv > 0.0 && bv >= rc.x) {
+            if (bv >= smem_max_pos(&S.rowC[i].x, bv)) wins += profile_update(prof + r0 + i, bv, c0 + bx) == bv;
         }
     }
+    wins = __reduce_add_sync(FULL, wins);
+    if (lane == 0) { S.stat[0] += nhits; S.stat[1] += wins; }
     __syncwarp();
-    return wins;
 }
 
 // ---------------------------------------------------------------------------------------------
-// Replay of one branch-free block.  The hot loop only remembers WHICH of its RB rows passed the filter (one bit
-// per row and lane) and the QT values at the start of the block.  When any lane of the warp has a bit set,
-// the block is walked again from that checkpoint with the same operands in the same order (bit-identical QT),
-// and the flagged thread-rows are parked in the hit buffer.  Warp-collective; returns the new hit count.
-// ---------------------------------------------------------------------------------------------
+// max of the filter keys of 8 values, optionally folded with a running maximum
+template <typename T>
+__device__ __forceinline__ int max_key8(const T *q) {
+    const int a = __vimax3_s32(key_of(q[0]), key_of(q[1]), key_of(q[2]));
+    const int b = __vimax3_s32(key_of(q[3]), key_of(q[4]), key_of(q[5]));
+    const int c = __vimax3_s32(key_of(q[6]), key_of(q[7]), a);
+    return max(b, c);
+}
+template <typename T>
+__device__ __forceinline__ int max_key8(const T *q, int run) {
+    const int a = __vimax3_s32(key_of(q[0]), key_of(q[1]), key_of(q[2]));
+    const int b = __vimax3_s32(key_of(q[3]), key_of(q[4]), key_of(q[5]));
+    const int c = __vimax3_s32(key_of(q[6]), key_of(q[7]), run);
+    return __vimax3_s32(a, b, c);
+}
+
 template <typename T> struct QVec { T v[DPT]; };
 
+// Row t of a replayed block: lanes whose thread-row passed the snapshot test (`cand`) compute the exact
+// P = (QT * inv_r) * inv_c of their 8 cells and compare it with the warp's live view of the column / row bests;
+// thread-rows with a real improvement park their QT values.  One shared copy of this code serves all 8 rows of
+// the unrolled replay (instruction-cache footprint).  Warp-collective; returns the new hit count.
+template <typename T>
+__device__ __noinline__ int park_row(QVec<T> q, bool cand, int t, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
+    const int lane = threadIdx.x & 31;
+    WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
+    const int i = i0 + t, e0 = i0 / DPT + lane;
+    bool flagged = false;
+    if (cand) {
+        const double2 rc = S.rowC[i];
+        const T ir = (T)rc.y;
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {                      // column i + DPT*lane + j
+            const int p = ((t + j) % DPT) * COL_STRIDE + e0 + (t + j) / DPT;
+            const double pv = (double)corr_of(q.v[j], ir, S.colW[p].x);
+            flagged |= pv > 0.0 && (pv >= S.colBest[p] || pv >= rc.x);
+        }
+    }
+    const unsigned mk = __ballot_sync(FULL, flagged);
+    if (mk) {
+        if (flagged) {
+            const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = q.v[j];
+            S.hitM[pos] = make_int2(i, i + DPT * lane);
+        }
+        hitcnt += __popc(mk);
+        if (hitcnt > HDRAIN) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }
+    }
+    return hitcnt;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Replay of one block.  The hot loop only knows that SOME cell of SOME lane's block passed the block-wide test.
+// The block is walked again from the QT values it started with -- same operands, same order, bit-identical QT --
+// and this time every cell's P = (QT * inv_r) * inv_c is formed (all lanes, 2 DMUL per cell) and its high word
+// compared, as an integer, with the high word of the warp's view of the column's best and of the row's best.
+// On smooth series (random walks) the QT-domain window tests are too loose to be worth an intermediate step:
+// P lives within a percent of the best for whole neighbourhoods, and only a per-cell test in the P domain tells
+// improvements from near misses.  Rows in which a lane passes go through park_row (exact compare + park).
+// Column operands slide through registers exactly as in the hot loop.  Warp-collective; returns the new hit count.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int hi_word(const double *p) { return reinterpret_cast<const int *>(p)[1]; }
+
 template <typename T, bool STRICT>
-__device__ __noinline__ int replay_block(QVec<T> qc, unsigned hm, int i0, int r0, int c0, int hitcnt, const T *__restrict__ inv,
-                                         const typename Tr<T>::T2 *__restrict__ nm, ProfileEntry *prof, unsigned *wins) {
+__device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
-    const unsigned any = __reduce_or_sync(FULL, hm);
-    const int last = 31 - __clz((int)any);                   // last flagged row of the block (any != 0)
-    for (int t = 0; t <= last; ++t) {
-        const int i = i0 + t;
-        const bool flagged = (hm >> t) & 1u;
-        const unsigned mk = __ballot_sync(FULL, flagged);
-        if (mk) {
-            if (flagged) {
-                const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
+    const int e0 = i0 / DPT + lane;                          // i0 is a multiple of DPT: class k of entry e0 is column i0 + DPT*lane + k
+    if (lane == 0) S.stat[2] += 1;
+    T cdf[DPT], cdg[DPT], civ[DPT];
+    int ckb[DPT];                                            // high word of the column's best (live view; >= 1 so that P <= 0 never passes)
 #pragma unroll
-                for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = qc.v[j];
-                S.hitM[pos] = make_int2(r0 + i, c0 + i + DPT * lane);
-            }
-            hitcnt += __popc(mk);
-            if (hitcnt > HDRAIN) { *wins += drain_hits<T>(hitcnt, r0, c0, inv, nm, prof); hitcnt = 0; }
+    for (int k = 0; k < DPT; ++k) {
+        const T2 a = S.colA[k * COL_STRIDE + e0];
+        cdf[k] = a.x; cdg[k] = a.y;
+        civ[k] = S.colW[k * COL_STRIDE + e0].x;
+        ckb[k] = max(hi_word(&S.colBest[k * COL_STRIDE + e0]), 1);
+    }
+#pragma unroll
+    for (int t = 0; t < RB; ++t) {
+        const int i = i0 + t;
+        const double2 rc = S.rowC[i];                        // {row's best, inv_r}
+        const T ir = (T)rc.y;
+        int kp[DPT];
+        bool cand = false;
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {
+            kp[j] = __double2hiint((double)corr_of(qc.v[j], ir, civ[(t + j) % DPT]));
+            cand |= kp[j] >= ckb[(t + j) % DPT];
         }
-        if (t < last) {
+        const int a = __vimax3_s32(kp[0], kp[1], kp[2]), b = __vimax3_s32(kp[3], kp[4], kp[5]);
+        cand |= __vimax3_s32(kp[6], kp[7], max(a, b)) >= max(__double2hiint(rc.x), 1);
+        if (__any_sync(FULL, cand)) hitcnt = park_row<T>(qc, cand, t, i0, r0, c0, hitcnt, prof);
+        if (t + 1 < RB) {
             const T2 ra = S.rowA[i + 1];
-            const int x = i + 1 + DPT * lane;
+            const T2 nd = S.colA[t * COL_STRIDE + e0 + 1];   // column entering the window: i + DPT*lane + DPT
+            cdf[t] = nd.x; cdg[t] = nd.y;
+            civ[t] = S.colW[t * COL_STRIDE + e0 + 1].x;
+            ckb[t] = max(hi_word(&S.colBest[t * COL_STRIDE + e0 + 1]), 1);
 #pragma unroll
             for (int j = 0; j < DPT; ++j) {
-                const T2 c = S.colA[col_slot(x + j)];
-                qc.v[j] = qt_step<STRICT>(qc.v[j], ra.x, ra.y, c.x, c.y);
+                const int k = (t + 1 + j) % DPT;
+                qc.v[j] = qt_step<STRICT>(qc.v[j], ra.x, ra.y, cdf[k], cdg[k]);
             }
         }
     }
@@ -272,20 +349,11 @@ __device__ __forceinline__ void reseed(T (&qt)[DPT], WarpSmem<T> &S, const doubl
     __syncwarp();   // A/U are about to be overwritten by the first tile
 }
 
-// max of the filter keys of FWIN = 8 values
-template <typename T>
-__device__ __forceinline__ int max_key8(const T *q) {
-    const int a = __vimax3_s32(key_of(q[0]), key_of(q[1]), key_of(q[2]));
-    const int b = __vimax3_s32(key_of(q[3]), key_of(q[4]), key_of(q[5]));
-    const int c = __vimax3_s32(key_of(q[6]), key_of(q[7]), a);
-    return max(b, c);
-}
-
 // item_start[lb] = first work item of this rank's local band lb (nlb + 1 entries)
-// counters[0] += thread-rows that passed the filter, counters[1] += profile slots improved
+// counters[0] += thread-rows parked for the exact test, counters[1] += profile slots improved, counters[2] += blocks replayed
 template <typename T, bool STRICT>
 __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
-tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ inv,
+tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ mnc,
             const T *__restrict__ qt0, const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
             const int *__restrict__ item_start, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
             unsigned long long *counters) {
@@ -314,7 +382,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
     }
 
     int hitcnt = 0;                 // warp-uniform: hits parked in the buffer
-    unsigned nhit = 0, nwin = 0;    // statistics
+    if (lane < 4) S.stat[lane] = 0;
     const T sl = slack(T(0));
 
     // Software pipeline: on entry to row i the registers hold QT(row i) already; the loop body takes the filter
@@ -327,8 +395,11 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 #pragma unroll
         for (int i = lane; i < ROWS_STAGED; i += 32) {
             S.rowA[i] = df_dg[r0 + i];
-            const T norm = nm[r0 + i].x;                        // +inf on the padding
-            const T best = max((T)__ldcg(&prof[r0 + i].corr), tiny_best(T(0)));   // never 0: 0 * inf would be a NaN
+            const T2 nv = nm[r0 + i];                           // {norm, inv}; norm = +inf on the padding
+            const T norm = nv.x;
+            const double rbest = __ldcg(&prof[r0 + i].corr);
+            S.rowC[i] = make_double2(rbest, (double)nv.y);
+            const T best = max((T)rbest, tiny_best(T(0)));      // never 0: 0 * inf would be a NaN
             T2 rb;
             rb.y = mul_rn(norm, sl);
             rb.x = mul_rn(best, rb.y);
@@ -338,29 +409,39 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         for (int x = lane; x < COL_WIN; x += 32) {
             const int p = col_slot(x);
             S.colA[p] = df_dg[c0 + x];
-            const T2 nv = nm[c0 + x];                       // {norm_c, min of norm over [c, c + FWIN)}
-            const T best = (T)__ldcg(&prof[c0 + x].corr);
+            const T2 nv = nm[c0 + x];                       // {norm_c, inv_c}
+            const double cbest = __ldcg(&prof[c0 + x].corr);
+            S.colBest[p] = cbest;
+            const T best = (T)cbest;
             T2 w;
-            w.x = nv.y;
+            w.x = nv.y;                                     // inv_c
             w.y = T(0);
             S.colW[p] = w;
             S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn(best, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
         }
+        for (int q = lane; q < WarpSmem<T>::NK; q += 32) S.mncK[q] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0));
         __syncwarp();
-        // window minima of the column keys: lane owns entry q (columns DPT*q .. DPT*q + DPT - 1) and needs entry q + 1
+        // minima of the row terms over each block of RB rows
+        if (lane < ROW_BLOCKS) {
+            T2 mn = S.rowB[RB * lane];
+#pragma unroll
+            for (int k = 1; k < RB; ++k) { const T2 v = S.rowB[RB * lane + k]; mn.x = min(mn.x, v.x); mn.y = min(mn.y, v.y); }
+            S.rowK[lane] = mn;
+        }
+        // minima of the column keys over the MNC_WIN = 15 columns starting at each column: lane owns entry q
+        // (columns DPT*q .. DPT*q + 7) and needs entries q + 1 and q + 2; beyond the staged window: +inf
         for (int q = lane; q < COL_STRIDE; q += 32) {
-            int a[DPT + FWIN];
+            int a[3 * DPT];
 #pragma unroll
-            for (int k = 0; k < DPT; ++k) a[k] = S.ck[k * COL_STRIDE + q];
+            for (int k = 0; k < 3 * DPT; ++k) a[k] = q + k / DPT < COL_STRIDE ? S.ck[(k % DPT) * COL_STRIDE + q + k / DPT] : key_of(pos_inf(T(0)));
 #pragma unroll
-            for (int k = 0; k < FWIN; ++k) a[DPT + k] = q + 1 < COL_STRIDE ? S.ck[k * COL_STRIDE + q + 1] : key_of(pos_inf(T(0)));
+            for (int k = 0; k < 3 * DPT - 1; ++k) a[k] = min(a[k], a[k + 1]);       // windows of 2
 #pragma unroll
-            for (int k = 0; k < DPT; ++k) {
-                int mn = a[k];
+            for (int k = 0; k < 3 * DPT - 3; ++k) a[k] = min(a[k], a[k + 2]);       // 4
 #pragma unroll
-                for (int e = 1; e < FWIN; ++e) mn = min(mn, a[k + e]);
-                set_key(S.colW[k * COL_STRIDE + q].y, mn);
-            }
+            for (int k = 0; k < 3 * DPT - 7; ++k) a[k] = min(a[k], a[k + 4]);       // 8
+#pragma unroll
+            for (int k = 0; k < DPT; ++k) set_key(S.colW[k * COL_STRIDE + q].y, min(a[k], a[k + MNC_WIN - 8]));   // 8 + 8 overlapping = 15
         }
         __syncwarp();
 
@@ -378,67 +459,46 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             first_tile = false;
         }
         const T2 *rowA = S.rowA + 2;                       // [ii] = {df, dg} of row i + 2 (consumed one sub-step later)
-        const T2 *rowB = S.rowB + 1;                       // [ii] = threshold terms of row i + 1
         const T2 *colA = S.colA + lane + 1;
-        const T2 *colW = S.colW + lane;
+        const T2 *colW = S.colW + lane;                    // [I] = window terms of the block: columns [DPT*I + DPT*lane, + MNC_WIN)
+        const T *mncK = S.mncK + lane;
         // operands of sub-step 0, loaded one sub-step ahead like all the others
         T2 ra = S.rowA[1];                                 // {df, dg} of row i + 1
-        T2 rb = S.rowB[0];                                 // threshold terms of row i
         T2 nd = colA[0];                                   // column entering the lane's window: x = i + DPT*lane + DPT
-        T2 cw[NWIN];                                       // window terms of row i: start y = i + DPT*lane + FWIN*w
-#pragma unroll
-        for (int w = 0; w < NWIN; ++w) cw[w] = colW[((FWIN * w) % DPT) * COL_STRIDE + (FWIN * w) / DPT];
 #pragma unroll 1
         for (int I = 0; I < TILE_H / DPT; ++I) {
-            QVec<T> qc;
-            unsigned hm = 0;
+            QVec<T> qc;                                    // QT at the start of the block (replay checkpoint)
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) qc.v[j] = qt[j];
+            const T2 rk = S.rowK[I];
+            const T cwn = mncK[I];
+            const T cww = colW[I].y;
+            int run = 0;
 #pragma unroll
             for (int ii = 0; ii < DPT; ++ii) {
-                if (ii % RB == 0) {
-#pragma unroll
-                    for (int j = 0; j < DPT; ++j) qc.v[j] = qt[j];
-                    hm = 0;
-                }
-                // operands of sub-step ii + 1
-                const T2 ra_n = rowA[ii];
-                const T2 rb_n = rowB[ii];
+                const T2 ra_n = rowA[ii];                  // operands of sub-step ii + 1
                 const T2 nd_n = colA[((ii + 1) % DPT) * COL_STRIDE + (ii + 1) / DPT];
-                T2 cw_n[NWIN];
-#pragma unroll
-                for (int w = 0; w < NWIN; ++w) cw_n[w] = colW[((ii + 1 + FWIN * w) % DPT) * COL_STRIDE + (ii + 1 + FWIN * w) / DPT];
-                // filter on QT(row i)
-                bool pass = false;
-#pragma unroll
-                for (int w = 0; w < NWIN; ++w) {
-                    const int ka = key_of(mul_rn(rb.x, cw[w].x));
-                    const int kb = key_of(mul_rn(rb.y, cw[w].y));
-                    pass |= max_key8(qt + FWIN * w) > __vimin_s32_relu(ka, kb);
-                }
-                hm |= pass ? (1u << (ii % RB)) : 0u;
-                // QT(row i + 1)
+                run = ii == 0 ? max_key8(qt) : max_key8(qt, run);      // keys of QT(row i)
                 cdf[ii] = nd.x; cdg[ii] = nd.y;
 #pragma unroll
                 for (int j = 0; j < DPT; ++j) {
                     const int k = (ii + 1 + j) % DPT;
-                    qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);
+                    qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);     // QT(row i + 1)
                 }
-                if (ii % RB == RB - 1) {
-                    if (__builtin_expect(__any_sync(FULL, hm != 0), 0)) {
-                        nhit += __reduce_add_sync(FULL, __popc(hm));
-                        hitcnt = replay_block<T, STRICT>(qc, hm, I * DPT + ii - (RB - 1), r0, c0, hitcnt, inv, nm, prof, &nwin);
-                    }
-                }
-                ra = ra_n; rb = rb_n; nd = nd_n;
-#pragma unroll
-                for (int w = 0; w < NWIN; ++w) cw[w] = cw_n[w];
+                ra = ra_n; nd = nd_n;
             }
-            rowA += DPT; rowB += DPT; colA += 1; colW += 1;
+            const int ka = key_of(mul_rn(rk.x, cwn));
+            const int kb = key_of(mul_rn(rk.y, cww));
+            if (__builtin_expect(__any_sync(FULL, run > __vimin_s32_relu(ka, kb)), 0))
+                hitcnt = replay_block<T, STRICT>(qc, I * DPT, r0, c0, hitcnt, prof);
+            rowA += DPT; colA += 1;
         }
-        if (hitcnt > 0) { nwin += drain_hits<T>(hitcnt, r0, c0, inv, nm, prof); hitcnt = 0; }   // hits never outlive their tile
+        if (hitcnt > 0) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }   // candidates never outlive their tile
     }
-    if (counters) {
-        nwin = __reduce_add_sync(FULL, nwin);
-        if (lane == 0 && nhit) { atomicAdd(counters, (unsigned long long)nhit); atomicAdd(counters + 1, (unsigned long long)nwin); }
+    __syncwarp();
+    if (counters && lane == 0 && S.stat[2]) {
+        atomicAdd(counters, (unsigned long long)S.stat[0]); atomicAdd(counters + 1, (unsigned long long)S.stat[1]);
+        atomicAdd(counters + 2, (unsigned long long)S.stat[2]);
     }
 }
 
@@ -480,7 +540,7 @@ int default_seg_rows(int sublen, int excl, int m, int world, int sm_count) {
 }
 
 template <typename T>
-static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *inv, const T *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *mnc, const T *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
     if (p.seg_rows % TILE_H != 0 || p.seg_rows < 0) return cudaErrorInvalidValue;
@@ -488,16 +548,16 @@ static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *inv, con
     auto kern = p.strict ? tile_kernel<T, true> : tile_kernel<T, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), inv, qt0, p.series, p.mu,
+    kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), mnc, qt0, p.series, p.mu,
                                                        prof, p.item_start, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters);
     return cudaGetLastError();
 }
 
-cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *inv, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
-    return launch_tiles_t<double>(df_dg, nm, inv, qt0, prof, p, s);
+cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *mnc, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    return launch_tiles_t<double>(df_dg, nm, mnc, qt0, prof, p, s);
 }
-cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *inv, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
-    return launch_tiles_t<float>(df_dg, nm, inv, qt0, prof, p, s);
+cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *mnc, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    return launch_tiles_t<float>(df_dg, nm, mnc, qt0, prof, p, s);
 }
 
 }  // namespace mpb

@@ -44,7 +44,7 @@ class MpbError(RuntimeError):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("precompute_ms", C.c_double), ("compute_ms", C.c_double), ("finalize_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("cells", C.c_int64), ("slow_updates", C.c_int64),
-                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64)]
+                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64), ("replays", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
