@@ -33,7 +33,7 @@ static_assert(sizeof(Aggregate<float>) == 8 && sizeof(InputDataPack<float>) == 1
 #define MPB_TILE_H 128
 #endif
 #ifndef MPB_WARPS
-#define MPB_WARPS 4
+#define MPB_WARPS 2
 #endif
 constexpr int DPT = MPB_DPT;              // diagonals per thread (register micro-tile width): 8 or 16
 constexpr int FWIN = 8;                   // columns a lane covers in one row

@@ -75,7 +75,7 @@ struct mpb_plan {
 extern "C" {
 
 const char *mpb_last_error(void) { return g_err; }
-const char *mpb_version(void) { return "mpb200 0.2 (sm_100a; tile kernel: DPT=8, BAND_W=1024, per-warp tiles of 128 rows, re-seeded row segments)"; }
+const char *mpb_version(void) { return "mpb200 0.4 (sm_100a; tile kernel: 8 diagonals per lane, 512-diagonal bands, per-warp tiles of 128 rows, block-wide QT-domain filter, re-seeded row segments)"; }
 
 int mpb_device_count(int *count) {
     if (!count) return fail(MPB_E_INVALID, "count is null");

@@ -67,40 +67,41 @@ template <typename T>
 struct WarpSmem {
     using T2 = typename Tr<T>::T2;
     static constexpr int NK = (COL_STRIDE + 3) / 4 * 4;
-    static constexpr int BYTES = 2 * ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + 2 * COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * 4 + COL_SLOTS * 8 +
-                                 HCAP * DPT * (int)sizeof(T) + HCAP * 8 + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + NK * (int)sizeof(T) + 16;
+    static constexpr int HITS_BYTES = HCAP * DPT * (int)sizeof(T) + HCAP * 8;
+    static constexpr int BYTES = ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * (int)sizeof(T) + COL_SLOTS * 8 +
+                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16;
     T2 *rowA;         // [i] = {df_r, dg_r}
-    T2 *rowB;         // [i] = {best_r * norm_r * s, norm_r * s},  s = 1 - 2^-18  (tile-start snapshot)
     double2 *rowC;    // [i] = {best correlation of the row as this warp knows it, inv_r}
     T2 *colA;         // [slot(x)] = {df_c, dg_c}
-    T2 *colW;         // [slot(y)] = {inv_y, min best_c * norm_c over the MNC_WIN columns starting at y (snapshot)}
-    int *ck;          // [slot(x)] = filter key of best_c * norm_c (input of the window minimum)
+    T *colInv;        // [slot(x)] = inv_c
     double *colBest;  // [slot(x)] = best correlation of the column as this warp knows it
     T *hitQ;          // [h][DPT] QT values of a parked thread-row
     int2 *hitM;       // [h] = {tile row i, window column x of its first cell}
-    T2 *rowK;         // [b] = minima of rowB over the rows [RB*b, RB*b + RB)
+    int *ck;          // staging scratch (aliases the empty hit buffer): [slot(x)] = filter key of best_c * norm_c
+    T2 *rowK;         // [b] = minima of {best_r * norm_r * s, norm_r * s} over the rows [RB*b, RB*b + RB),  s = 1 - 2^-18
     T *mncK;          // [q] = min of norm over the MNC_WIN columns starting at window column DPT*q
-    unsigned *stat;   // [0] candidates parked, [1] profile slots improved, [2] blocks replayed
+    T *wK;            // [q] = min of best_c * norm_c over the same columns (key precision)
+    unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] blocks replayed
     __device__ __forceinline__ explicit WarpSmem(unsigned char *base) {
         rowA = reinterpret_cast<T2 *>(base);
-        rowB = rowA + ROWS_STAGED;
-        rowC = reinterpret_cast<double2 *>(rowB + ROWS_STAGED);
+        rowC = reinterpret_cast<double2 *>(rowA + ROWS_STAGED);
         colA = reinterpret_cast<T2 *>(rowC + ROWS_STAGED);
-        colW = colA + COL_SLOTS;
-        ck = reinterpret_cast<int *>(colW + COL_SLOTS);
-        colBest = reinterpret_cast<double *>(ck + COL_SLOTS);
+        colInv = reinterpret_cast<T *>(colA + COL_SLOTS);
+        colBest = reinterpret_cast<double *>(colInv + COL_SLOTS);
         hitQ = reinterpret_cast<T *>(colBest + COL_SLOTS);
         hitM = reinterpret_cast<int2 *>(hitQ + HCAP * DPT);
+        ck = reinterpret_cast<int *>(hitQ);
         rowK = reinterpret_cast<T2 *>(hitM + HCAP);
         mncK = reinterpret_cast<T *>(rowK + (ROW_BLOCKS + 1) / 2 * 2);
-        stat = reinterpret_cast<unsigned *>(mncK + NK);
+        wK = mncK + NK;
+        stat = reinterpret_cast<unsigned *>(wK + NK);
     }
 };
 static_assert(WarpSmem<double>::BYTES % 16 == 0 && WarpSmem<float>::BYTES % 16 == 0, "warp slices stay 16-byte aligned");
-static_assert((ROWS_STAGED * sizeof(float2)) % 16 == 0 && (COL_SLOTS * sizeof(float2)) % 16 == 0 && (COL_SLOTS * 4) % 16 == 0 &&
-              (COL_SLOTS * 8) % 16 == 0, "sub-arrays stay 16-byte aligned");
-static_assert(2 * ROWS_STAGED * sizeof(float2) >= SEED_KC * sizeof(double), "seed operand A aliases rowA/rowB");
-static_assert(2 * COL_SLOTS * sizeof(float2) >= COL_SLOTS * sizeof(double), "seed window U aliases colA/colW");
+static_assert((ROWS_STAGED * sizeof(float2)) % 16 == 0 && (COL_SLOTS * sizeof(float)) % 16 == 0 && (HCAP * DPT * sizeof(float)) % 16 == 0, "sub-arrays stay 16-byte aligned");
+static_assert(WarpSmem<float>::HITS_BYTES >= COL_SLOTS * 4, "the column-key scratch fits the hit buffer");
+static_assert(ROWS_STAGED * sizeof(float2) >= SEED_KC * sizeof(double), "seed operand A aliases rowA");
+static_assert(COL_SLOTS * sizeof(float2) >= COL_SLOTS * sizeof(double), "seed window U aliases colA");
 static_assert(SEED_KC + WARP_DIAGS + DPT <= COL_WIN && SEED_KC % DPT == 0, "seed window fits the column slots");
 
 template <typename T> constexpr int cta_smem_bytes() { return BAND_WARPS * WarpSmem<T>::BYTES; }
@@ -169,7 +170,7 @@ __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry 
         const int i = mt.x, x = mt.y + j;
         const int p = col_slot(x);
         const double2 rc = S.rowC[i];
-        double pv = (double)corr_of(S.hitQ[h * DPT + j], (T)rc.y, S.colW[p].x);
+        double pv = (double)corr_of(S.hitQ[h * DPT + j], (T)rc.y, S.colInv[p]);
         if (!act || !(pv > 0.0)) pv = -1.0;                  // P <= 0 and NaN never enter the profile (it starts at +0.0)
         if (pv > 0.0 && pv >= S.colBest[p]) {
             if (pv >= smem_max_pos(&S.colBest[p], pv)) wins += profile_update(prof + c0 + x, pv, r0 + i) == pv;
@@ -226,7 +227,7 @@ __device__ __noinline__ int park_row(QVec<T> q, bool cand, int t, int i0, int r0
 #pragma unroll
         for (int j = 0; j < DPT; ++j) {                      // column i + DPT*lane + j
             const int p = ((t + j) % DPT) * COL_STRIDE + e0 + (t + j) / DPT;
-            const double pv = (double)corr_of(q.v[j], ir, S.colW[p].x);
+            const double pv = (double)corr_of(q.v[j], ir, S.colInv[p]);
             flagged |= pv > 0.0 && (pv >= S.colBest[p] || pv >= rc.x);
         }
     }
@@ -269,7 +270,7 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
     for (int k = 0; k < DPT; ++k) {
         const T2 a = S.colA[k * COL_STRIDE + e0];
         cdf[k] = a.x; cdg[k] = a.y;
-        civ[k] = S.colW[k * COL_STRIDE + e0].x;
+        civ[k] = S.colInv[k * COL_STRIDE + e0];
         ckb[k] = max(hi_word(&S.colBest[k * COL_STRIDE + e0]), 1);
     }
 #pragma unroll
@@ -291,7 +292,7 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
             const T2 ra = S.rowA[i + 1];
             const T2 nd = S.colA[t * COL_STRIDE + e0 + 1];   // column entering the window: i + DPT*lane + DPT
             cdf[t] = nd.x; cdg[t] = nd.y;
-            civ[t] = S.colW[t * COL_STRIDE + e0 + 1].x;
+            civ[t] = S.colInv[t * COL_STRIDE + e0 + 1];
             ckb[t] = max(hi_word(&S.colBest[t * COL_STRIDE + e0 + 1]), 1);
 #pragma unroll
             for (int j = 0; j < DPT; ++j) {
@@ -312,8 +313,8 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
 template <typename T>
 __device__ __forceinline__ void reseed(T (&qt)[DPT], WarpSmem<T> &S, const double *__restrict__ Tser, const double *__restrict__ mu,
                                        int n, int m, int sublen, int rs, int d0w, int lane) {
-    double *A = reinterpret_cast<double *>(S.rowA);      // aliases rowA/rowB
-    double *U = reinterpret_cast<double *>(S.colA);      // aliases colA/colW (de-interleaved like the columns)
+    double *A = reinterpret_cast<double *>(S.rowA);      // aliases rowA
+    double *U = reinterpret_cast<double *>(S.colA);      // aliases colA (de-interleaved like the columns)
     const double mur = mu[rs];
     const double muref = mu[min(rs + d0w, sublen - 1)];
     double acc[DPT], sumA = 0.0;
@@ -393,17 +394,25 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         const int c0 = r0 + d0w;
         __syncwarp();   // previous tile fully consumed
 #pragma unroll
-        for (int i = lane; i < ROWS_STAGED; i += 32) {
-            S.rowA[i] = df_dg[r0 + i];
-            const T2 nv = nm[r0 + i];                           // {norm, inv}; norm = +inf on the padding
-            const T norm = nv.x;
-            const double rbest = __ldcg(&prof[r0 + i].corr);
-            S.rowC[i] = make_double2(rbest, (double)nv.y);
-            const T best = max((T)rbest, tiny_best(T(0)));      // never 0: 0 * inf would be a NaN
+        for (int i0s = 0; i0s < ROWS_STAGED; i0s += 32) {  // rows: operands, the warp's view of their best, block minima of the threshold terms
+            const int i = i0s + lane;
             T2 rb;
-            rb.y = mul_rn(norm, sl);
-            rb.x = mul_rn(best, rb.y);
-            S.rowB[i] = rb;
+            rb.x = rb.y = pos_inf(T(0));
+            if (i < ROWS_STAGED) {
+                S.rowA[i] = df_dg[r0 + i];
+                const T2 nv = nm[r0 + i];                       // {norm, inv}; norm = +inf on the padding
+                const double rbest = __ldcg(&prof[r0 + i].corr);
+                S.rowC[i] = make_double2(rbest, (double)nv.y);
+                const T best = max((T)rbest, tiny_best(T(0)));  // never 0: 0 * inf would be a NaN
+                rb.y = mul_rn(nv.x, sl);
+                rb.x = mul_rn(best, rb.y);
+            }
+#pragma unroll
+            for (int sft = 1; sft < RB; sft <<= 1) {            // minima over each block of RB = 8 consecutive rows (8 adjacent lanes)
+                rb.x = min(rb.x, __shfl_xor_sync(FULL, rb.x, sft));
+                rb.y = min(rb.y, __shfl_xor_sync(FULL, rb.y, sft));
+            }
+            if (lane % RB == 0 && i < ROWS_STAGED) S.rowK[i / RB] = rb;
         }
 #pragma unroll 4
         for (int x = lane; x < COL_WIN; x += 32) {
@@ -412,36 +421,22 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             const T2 nv = nm[c0 + x];                       // {norm_c, inv_c}
             const double cbest = __ldcg(&prof[c0 + x].corr);
             S.colBest[p] = cbest;
-            const T best = (T)cbest;
-            T2 w;
-            w.x = nv.y;                                     // inv_c
-            w.y = T(0);
-            S.colW[p] = w;
-            S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn(best, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
+            S.colInv[p] = nv.y;
+            S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn((T)cbest, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
         }
         for (int q = lane; q < WarpSmem<T>::NK; q += 32) S.mncK[q] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0));
         __syncwarp();
-        // minima of the row terms over each block of RB rows
-        if (lane < ROW_BLOCKS) {
-            T2 mn = S.rowB[RB * lane];
-#pragma unroll
-            for (int k = 1; k < RB; ++k) { const T2 v = S.rowB[RB * lane + k]; mn.x = min(mn.x, v.x); mn.y = min(mn.y, v.y); }
-            S.rowK[lane] = mn;
-        }
-        // minima of the column keys over the MNC_WIN = 15 columns starting at each column: lane owns entry q
-        // (columns DPT*q .. DPT*q + 7) and needs entries q + 1 and q + 2; beyond the staged window: +inf
+        // minima of the column keys over the MNC_WIN = 15 columns of each block window: lane owns window q
+        // (columns DPT*q .. DPT*q + 14 = all of entry q, classes 0..6 of entry q + 1); beyond the staged window: +inf
         for (int q = lane; q < COL_STRIDE; q += 32) {
-            int a[3 * DPT];
+            int mn = S.ck[q];
 #pragma unroll
-            for (int k = 0; k < 3 * DPT; ++k) a[k] = q + k / DPT < COL_STRIDE ? S.ck[(k % DPT) * COL_STRIDE + q + k / DPT] : key_of(pos_inf(T(0)));
+            for (int k = 1; k < DPT; ++k) mn = min(mn, S.ck[k * COL_STRIDE + q]);
+            if (q + 1 < COL_STRIDE) {
 #pragma unroll
-            for (int k = 0; k < 3 * DPT - 1; ++k) a[k] = min(a[k], a[k + 1]);       // windows of 2
-#pragma unroll
-            for (int k = 0; k < 3 * DPT - 3; ++k) a[k] = min(a[k], a[k + 2]);       // 4
-#pragma unroll
-            for (int k = 0; k < 3 * DPT - 7; ++k) a[k] = min(a[k], a[k + 4]);       // 8
-#pragma unroll
-            for (int k = 0; k < DPT; ++k) set_key(S.colW[k * COL_STRIDE + q].y, min(a[k], a[k + MNC_WIN - 8]));   // 8 + 8 overlapping = 15
+                for (int k = 0; k < MNC_WIN - DPT; ++k) mn = min(mn, S.ck[k * COL_STRIDE + q + 1]);
+            }
+            set_key(S.wK[q], mn);
         }
         __syncwarp();
 
@@ -460,8 +455,8 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         }
         const T2 *rowA = S.rowA + 2;                       // [ii] = {df, dg} of row i + 2 (consumed one sub-step later)
         const T2 *colA = S.colA + lane + 1;
-        const T2 *colW = S.colW + lane;                    // [I] = window terms of the block: columns [DPT*I + DPT*lane, + MNC_WIN)
-        const T *mncK = S.mncK + lane;
+        const T *mncK = S.mncK + lane;                     // [I] = window terms of the block: columns [DPT*I + DPT*lane, + MNC_WIN)
+        const T *wK = S.wK + lane;
         // operands of sub-step 0, loaded one sub-step ahead like all the others
         T2 ra = S.rowA[1];                                 // {df, dg} of row i + 1
         T2 nd = colA[0];                                   // column entering the lane's window: x = i + DPT*lane + DPT
@@ -472,7 +467,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             for (int j = 0; j < DPT; ++j) qc.v[j] = qt[j];
             const T2 rk = S.rowK[I];
             const T cwn = mncK[I];
-            const T cww = colW[I].y;
+            const T cww = wK[I];
             int run = 0;
 #pragma unroll
             for (int ii = 0; ii < DPT; ++ii) {
