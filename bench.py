@@ -201,7 +201,7 @@ def run_gpu_arm(args):
     corr_buf = torch.empty(sublen, dtype=torch.float64, device="cuda")
     index_buf = torch.empty(sublen, dtype=torch.int32, device="cuda")
     if world > 1:
-        from mpb200.dist import merge_plan_across_ranks
+        from mpb200.dist import compute_merged
         with torch.cuda.stream(stream):
             dist.all_reduce(index_buf)          # communicator creation stays outside the timed region
         ctx.finish()
@@ -215,11 +215,11 @@ def run_gpu_arm(args):
             if e2e:
                 plan.upload_series_ptr(T_pinned.data_ptr())
             plan.precompute()
-            plan.compute()
             extra = 0
             if world > 1:
-                merge_plan_across_ranks(plan, corr_buf, index_buf)
-                extra = 3                                           # export, mask_index, import kernels
+                extra = compute_merged(plan, corr_buf, index_buf, world)   # first bands, merge, remaining bands, merge
+            else:
+                plan.compute()
             plan.finalize()
             if e2e:
                 plan.download_into(MP_pinned.data_ptr(), MPI_pinned.data_ptr())

@@ -38,6 +38,7 @@ extern "C" {
                                   bit-identical to the reference kernels' chain, 6 instead of 4 FP64 ops per cell */
 #define MPB_FLAG_SEQ_MEAN 2u   /* mu by the reference's sequential running-mean recurrence (HostSideComputation.hpp:29) */
 #define MPB_FLAG_NO_RESEED 4u  /* one full-length chain per diagonal, seeded at row 0 only (Vanilla.cpp:43-55) */
+#define MPB_FLAG_NO_SEED 8u    /* do not pre-load the profile with the lag-m/4 diagonal (measurement aid; results are the same) */
 
 typedef struct mpb_context mpb_context; /* replaces OpenCL::Context   (OpenCL.hpp:73-107, 294-317) */
 typedef struct mpb_buffer mpb_buffer;   /* replaces OpenCL::Buffer<T> (OpenCL.hpp:109-211) */
@@ -121,6 +122,12 @@ int mpb_plan_upload_series(mpb_plan *plan, const double *T_host);   /* async H2D
 void *mpb_plan_series_device_ptr(mpb_plan *plan);                   /* double[n] in HBM, caller may fill it */
 int mpb_plan_precompute(mpb_plan *plan);                            /* kernel (1) */
 int mpb_plan_compute(mpb_plan *plan);                               /* kernel (2) over this rank's bands */
+/* The same in pieces: local bands [lb_begin, lb_end) of this rank (lb_end < 0 = all). A multi-GPU job walks a few
+ * bands, max-merges the profiles across ranks (export / mask_index / import below), then walks the rest: the filter
+ * thresholds of every rank then come from all ranks' first bands instead of its own only. lb_begin == 0 starts the
+ * step's compute timer and statistics. */
+int mpb_plan_compute_bands(mpb_plan *plan, int lb_begin, int lb_end);
+int mpb_plan_local_bands(mpb_plan *plan, int *count);                /* number of diagonal bands this rank walks */
 /* Split the packed (corr, index) profile into two dense device arrays for an external max-reduction
  * (NCCL through torch.distributed): corr_out float64[n-m+1] (non-negative, so its int64 bit pattern is
  * order-preserving), index_out int32[n-m+1]. */

@@ -16,6 +16,9 @@ cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, fl
 cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, double *mnc, cudaStream_t s);
 cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, float *mnc, cudaStream_t s);
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s);
+// seeds every profile slot with the cell at lag `lag` (the first diagonal outside the exclusion zone), computed directly
+cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s);
+cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s);
 cudaError_t launch_pack_input_f64(const double *df_dg, const double *inv, const double *qt0, int sublen, void *out, cudaStream_t s);
 cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const float *qt0, int sublen, void *out, cudaStream_t s);
 
@@ -27,7 +30,8 @@ struct TileLaunch {
     const double *series, *mu;          // T[n], mu[sublen] (re-seed operands)
     const int *item_start;              // device: prefix table (nlb + 1 entries) followed by the band ids in visiting order (nlb entries)
     int nlb;                            // this rank's band count
-    long long items;                    // total work items (= grid size)
+    long long items;                    // work items of this launch (= grid size)
+    int item_begin;                     // first work item of this launch (index into the prefix table)
     unsigned long long *counters;       // device: [0] cells parked, [1] profile slots improved, [2] blocks replayed (may be null)
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem

@@ -164,6 +164,43 @@ __global__ void norm_kernel(const OutT *__restrict__ inv, int sublen, int np, Ou
     mnc[i] = mn;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Seed profile: the first diagonal outside the exclusion zone (lag m/4), every cell from its own centred dot
+// product, P = (QT * inv_i) * inv_j (kernel/MatrixProfileKernelVanilla.cpp:84), applied to both the row's and the
+// column's slot.  These are ordinary cells of the matrix (the tile kernel computes them again), so the result is
+// unchanged; but subsequences at lag m/4 overlap in 3m/4 samples, so every slot starts from a high correlation
+// and the tile kernel's filter rejects almost everything from its first row on -- on every GPU alike, whichever
+// bands it owns.  Cost: m FMAs per subsequence (about 0.1 ms at n = 2^20).  Skipped in MPB_FLAG_STRICT, where the
+// value must carry the reference chain's exact rounding.
+// ---------------------------------------------------------------------------------------------
+template <typename OutT>
+__global__ void __launch_bounds__(STATS_THREADS)
+seed_profile_kernel(const double *__restrict__ T, const double *__restrict__ mu, const OutT *__restrict__ inv, int n, int m, int lag,
+                    ProfileEntry *prof) {
+    extern __shared__ double sm[];                   // T[i0 .. i0 + STATS_THREADS + m + lag)
+    const int sublen = n - m + 1;
+    const int i0 = blockIdx.x * STATS_THREADS;
+    for (int k = threadIdx.x; k < STATS_THREADS + m + lag; k += STATS_THREADS) sm[k] = (i0 + k < n) ? T[i0 + k] : 0.0;
+    __syncthreads();
+    const int i = i0 + threadIdx.x, j = i + lag;
+    if (j >= sublen) return;
+    const double mi = mu[i], mj = mu[j];
+    const double *a = sm + threadIdx.x, *b = a + lag;
+    double q0 = 0.0, q1 = 0.0;
+    int k = 0;
+    for (; k + 1 < m; k += 2) {
+        q0 = fma(a[k] - mi, b[k] - mj, q0);
+        q1 = fma(a[k + 1] - mi, b[k + 1] - mj, q1);
+    }
+    if (k < m) q0 = fma(a[k] - mi, b[k] - mj, q0);
+    const OutT qt = (OutT)(q0 + q1);
+    const double p = (double)((qt * inv[i]) * inv[j]);
+    if (p > 0.0) {
+        profile_update(prof + i, p, j);
+        profile_update(prof + j, p, i);
+    }
+}
+
 __global__ void profile_init_kernel(ProfileEntry *prof, int count) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) { ProfileEntry e; e.corr = 0.0; e.index = -1; e.pad = 0; prof[i] = e; }
@@ -217,6 +254,24 @@ cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, d
 cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, float *mnc, cudaStream_t s) {
     norm_kernel<float><<<(np + 255) / 256, 256, 0, s>>>(inv, sublen, np, nm, mnc);
     return cudaGetLastError();
+}
+template <typename OutT>
+static cudaError_t launch_seed_t(const double *T, const double *mu, const OutT *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s) {
+    const int sublen = n - m + 1;
+    if (sublen - lag <= 0) return cudaSuccess;
+    const size_t smem = sizeof(double) * (size_t)(STATS_THREADS + m + lag);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(seed_profile_kernel<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    seed_profile_kernel<OutT><<<(sublen - lag + STATS_THREADS - 1) / STATS_THREADS, STATS_THREADS, smem, s>>>(T, mu, inv, n, m, lag, prof);
+    return cudaGetLastError();
+}
+cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s) {
+    return launch_seed_t<double>(T, mu, inv, n, m, lag, prof, s);
+}
+cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s) {
+    return launch_seed_t<float>(T, mu, inv, n, m, lag, prof, s);
 }
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s) {
     profile_init_kernel<<<(count + 255) / 256, 256, 0, s>>>(prof, count);

@@ -67,6 +67,7 @@ struct mpb_plan {
     int nlb = 0;
     long long items = 0;
     bool table_dirty = true;
+    std::vector<int> table_host;          // host copy of the work-item table (prefix sums, then band ids)
     cudaEvent_t ev[8] = {};
     mpb_timings tm = {};
     bool ran_h2d = false;
@@ -320,6 +321,7 @@ static int plan_build_table(mpb_plan *p) {
     if (p->item_start) { cudaFree(p->item_start); p->item_start = nullptr; }
     CU(cudaMalloc((void **)&p->item_start, sizeof(int) * tab.size()));
     CU(cudaMemcpy(p->item_start, tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice));
+    p->table_host = tab;
     p->nlb = ((int)tab.size() - 1) / 2; p->items = items; p->seg_rows_eff = seg; p->table_dirty = false;
     return MPB_OK;
 }
@@ -350,33 +352,55 @@ int mpb_plan_precompute(mpb_plan *p) {
     if (p->dtype == MPB_F64) CU(mpb::launch_norm_f64((const double *)p->inv, p->sublen, p->np, (double *)p->nm, (double *)p->mnc, s));
     else CU(mpb::launch_norm_f32((const float *)p->inv, p->sublen, p->np, (float *)p->nm, (float *)p->mnc, s));
     CU(mpb::launch_profile_init(p->prof, p->np, s));
-    CU(cudaEventRecord(p->ev[3], s));
     p->tm.launches = 4;
+    if (!(p->flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_SEED))) {
+        if (p->dtype == MPB_F64) CU(mpb::launch_seed_profile_f64(p->T, p->mu, (const double *)p->inv, p->n, p->m, p->excl, p->prof, s));
+        else CU(mpb::launch_seed_profile_f32(p->T, p->mu, (const float *)p->inv, p->n, p->m, p->excl, p->prof, s));
+        p->tm.launches += 1;
+    }
+    CU(cudaEventRecord(p->ev[3], s));
     return MPB_OK;
 }
 
-int mpb_plan_compute(mpb_plan *p) {
+int mpb_plan_local_bands(mpb_plan *p, int *count) {
+    if (!p || !count) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    int rc = plan_build_table(p);
+    if (rc != MPB_OK) return rc;
+    *count = p->nlb;
+    return MPB_OK;
+}
+
+int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     cudaStream_t s = p->ctx->stream;
     CU(cudaSetDevice(p->ctx->device));
     int rc = plan_build_table(p);
     if (rc != MPB_OK) return rc;
+    if (lb_end < 0 || lb_end > p->nlb) lb_end = p->nlb;
+    if (lb_begin < 0 || lb_begin > lb_end) return fail(MPB_E_INVALID, "bad local band range [%d, %d) of %d", lb_begin, lb_end, p->nlb);
     mpb::TileLaunch tl;
     tl.n = p->n; tl.m = p->m; tl.sublen = p->sublen; tl.excl = p->excl; tl.rank = p->rank; tl.world = p->world;
     tl.seg_rows = p->seg_rows_eff;
     tl.strict = (p->flags & MPB_FLAG_STRICT) != 0;
     tl.series = p->T; tl.mu = p->mu;
-    tl.item_start = p->item_start; tl.nlb = p->nlb; tl.items = p->items;
+    tl.item_start = p->item_start; tl.nlb = p->nlb;
+    tl.item_begin = p->nlb > 0 ? p->table_host[lb_begin] : 0;
+    tl.items = p->nlb > 0 ? (long long)p->table_host[lb_end] - tl.item_begin : 0;
     tl.counters = p->slow_counter;
-    CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
-    CU(cudaEventRecord(p->ev[4], s));
+    if (lb_begin == 0) {                      // first launch of a step: statistics and the compute timer start here
+        CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
+        CU(cudaEventRecord(p->ev[4], s));
+        p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
+    }
     if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->mnc, (const double *)p->qt0, p->prof, tl, s));
     else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->mnc, (const float *)p->qt0, p->prof, tl, s));
     CU(cudaEventRecord(p->ev[5], s));
-    p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
-    p->tm.launches += p->items > 0 ? 1 : 0;
+    p->tm.launches += tl.items > 0 ? 1 : 0;
     return MPB_OK;
 }
+
+int mpb_plan_compute(mpb_plan *p) { return mpb_plan_compute_bands(p, 0, -1); }
 
 int mpb_plan_export(mpb_plan *p, void *corr_out, void *index_out) {
     if (!p || !corr_out || !index_out) return fail(MPB_E_INVALID, "null argument");

@@ -356,7 +356,7 @@ template <typename T, bool STRICT>
 __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ mnc,
             const T *__restrict__ qt0, const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
-            const int *__restrict__ item_start, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
+            const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
             unsigned long long *counters) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -364,7 +364,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 
     // work item -> (local band, segment): binary search in the prefix table
     int lo = 0, hi = nlb;
-    const int item = blockIdx.x;
+    const int item = blockIdx.x + item_begin;
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
     const int seg = item - item_start[lo];
     const int band = item_start[nlb + 1 + lo];                  // band ids follow the prefix table
@@ -544,7 +544,7 @@ static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *mnc, con
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), mnc, qt0, p.series, p.mu,
-                                                       prof, p.item_start, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters);
+                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters);
     return cudaGetLastError();
 }
 

@@ -19,7 +19,7 @@ import weakref
 import numpy as np
 
 F64, F32 = 0, 1
-FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED = 1, 2, 4
+FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED, FLAG_NO_SEED = 1, 2, 4, 8
 _LIB = None
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # matrix-profile-hls_b200/
 LIB_PATH = os.environ.get("MPB200_LIB") or os.path.join(_PKG_ROOT, "libmpb200.so")   # MPB200_LIB: tuning builds (csrc/Makefile VARIANT=)
@@ -55,7 +55,7 @@ EXPORTS = [
     "mpb_context_stream", "mpb_context_device", "mpb_buffer_create", "mpb_buffer_destroy", "mpb_buffer_copy_from_host",
     "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_upload_series",
-    "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_export", "mpb_plan_mask_index",
+    "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
     "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_useful_cells", "mpb_measure_fma_peak",
 ]
@@ -241,6 +241,15 @@ class Plan:
 
     def compute(self):
         _chk(lib().mpb_plan_compute(self._h))
+
+    def compute_bands(self, lb_begin, lb_end=-1):
+        """Kernel (2) over local bands [lb_begin, lb_end) only (lb_end < 0 = to the end)."""
+        _chk(lib().mpb_plan_compute_bands(self._h, C.c_int(lb_begin), C.c_int(lb_end)))
+
+    def local_bands(self):
+        c = C.c_int(0)
+        _chk(lib().mpb_plan_local_bands(self._h, C.byref(c)))
+        return c.value
 
     def export(self, corr_ptr, index_ptr):
         _chk(lib().mpb_plan_export(self._h, C.c_void_p(corr_ptr), C.c_void_p(index_ptr)))

@@ -46,3 +46,27 @@ def merge_plan_across_ranks(plan, corr_buf, index_buf, group=None):
 
     allreduce_profile(corr_buf, index_buf, mask_fn=mask, group=group)
     plan.import_(corr_buf.data_ptr(), index_buf.data_ptr())
+
+
+WARM_BANDS_TOTAL = 48     # diagonal bands (512 diagonals each) after which the filter thresholds are tight
+
+
+def compute_merged(plan, corr_buf, index_buf, world, group=None):
+    """The multi-GPU compute step: every rank walks its first few bands, the profiles are max-merged (so that each
+    rank's filter thresholds come from ALL ranks' first bands, about WARM_BANDS_TOTAL in total, instead of its own
+    few), then every rank walks the rest of its bands and the profiles are merged again.  Returns the number of
+    kernels launched besides the tile kernel."""
+    nlb = plan.local_bands()
+    warm = min(nlb, max(1, -(-WARM_BANDS_TOTAL // world)))
+    extra = 0
+    if world > 1 and warm < nlb:
+        plan.compute_bands(0, warm)
+        merge_plan_across_ranks(plan, corr_buf, index_buf, group=group)
+        plan.compute_bands(warm, -1)
+        extra += 3
+    else:
+        plan.compute_bands(0, -1)
+    if world > 1:
+        merge_plan_across_ranks(plan, corr_buf, index_buf, group=group)
+        extra += 3
+    return extra
