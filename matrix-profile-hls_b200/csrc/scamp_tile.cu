@@ -63,13 +63,16 @@ constexpr int ROW_BLOCKS = ROWS_STAGED / RB;
 constexpr int COL_SLOTS = DPT * COL_STRIDE;
 constexpr unsigned FULL = 0xffffffffu;
 
+struct __align__(16) Winner { double v; int slot; int idx; };
+constexpr int WCAP = 40;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners)
+
 template <typename T>
 struct WarpSmem {
     using T2 = typename Tr<T>::T2;
     static constexpr int NK = (COL_STRIDE + 3) / 4 * 4;
     static constexpr int HITS_BYTES = HCAP * DPT * (int)sizeof(T) + HCAP * 8;
     static constexpr int BYTES = ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * (int)sizeof(T) + COL_SLOTS * 8 +
-                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16;
+                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16 + WCAP * 16;
     T2 *rowA;         // [i] = {df_r, dg_r}
     double2 *rowC;    // [i] = {best correlation of the row as this warp knows it, inv_r}
     T2 *colA;         // [slot(x)] = {df_c, dg_c}
@@ -82,6 +85,7 @@ struct WarpSmem {
     T *mncK;          // [q] = min of norm over the MNC_WIN columns starting at window column DPT*q
     T *wK;            // [q] = min of best_c * norm_c over the same columns (key precision)
     unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] blocks replayed
+    Winner *wlist;    // cells that improved the warp's view of a slot, waiting for the profile update
     __device__ __forceinline__ explicit WarpSmem(unsigned char *base) {
         rowA = reinterpret_cast<T2 *>(base);
         rowC = reinterpret_cast<double2 *>(rowA + ROWS_STAGED);
@@ -95,6 +99,7 @@ struct WarpSmem {
         mncK = reinterpret_cast<T *>(rowK + (ROW_BLOCKS + 1) / 2 * 2);
         wK = mncK + NK;
         stat = reinterpret_cast<unsigned *>(wK + NK);
+        wlist = reinterpret_cast<Winner *>(stat + 4);
     }
 };
 static_assert(WarpSmem<double>::BYTES % 16 == 0 && WarpSmem<float>::BYTES % 16 == 0, "warp slices stay 16-byte aligned");
@@ -154,13 +159,25 @@ __device__ __forceinline__ double smem_max_pos(double *addr, double v) {
 // thread-row -- of the row's best.  Only cells that improve that view touch the profile in HBM/L2, with a 128-bit
 // compare-and-swap (mp_common.cuh: larger corr wins, equal corr -> smaller index).  Warp-collective.
 // ---------------------------------------------------------------------------------------------
+// applies the winner list to the profile: one entry per lane, so the memory round trips of a whole batch overlap
+template <typename T>
+__device__ __forceinline__ unsigned apply_winners(WarpSmem<T> &S, int cnt, ProfileEntry *prof, int lane) {
+    unsigned wins = 0;
+    __syncwarp();
+    for (int e = lane; e < cnt; e += 32) { const Winner w = S.wlist[e]; wins += profile_update(prof + w.slot, w.v, w.idx) == w.v; }
+    __syncwarp();
+    return wins;
+}
+
 template <typename T>
 __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry *prof) {
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
     __syncwarp();
     unsigned wins = 0;
+    int wcnt = 0;                                            // warp-uniform
     const int ncell = nhits * DPT;
+    const unsigned lt = (1u << lane) - 1u;
 #pragma unroll 1
     for (int base = 0; base < ncell; base += 32) {
         const int e = base + lane;
@@ -172,9 +189,8 @@ __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry 
         const double2 rc = S.rowC[i];
         double pv = (double)corr_of(S.hitQ[h * DPT + j], (T)rc.y, S.colInv[p]);
         if (!act || !(pv > 0.0)) pv = -1.0;                  // P <= 0 and NaN never enter the profile (it starts at +0.0)
-        if (pv > 0.0 && pv >= S.colBest[p]) {
-            if (pv >= smem_max_pos(&S.colBest[p], pv)) wins += profile_update(prof + c0 + x, pv, r0 + i) == pv;
-        }
+        bool cwin = pv > 0.0 && pv >= S.colBest[p];
+        if (cwin) cwin = pv >= smem_max_pos(&S.colBest[p], pv);
         double bv = pv;                                      // best of the thread-row; ties keep the smaller column
         int bx = x;
 #pragma unroll
@@ -183,10 +199,18 @@ __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry 
             const int ox = __shfl_xor_sync(FULL, bx, sft);
             if (ov > bv || (ov == bv && ox < bx)) { bv = ov; bx = ox; }
         }
-        if (j == 0 && bv > 0.0 && bv >= rc.x) {
-            if (bv >= smem_max_pos(&S.rowC[i].x, bv)) wins += profile_update(prof + r0 + i, bv, c0 + bx) == bv;
+        bool rwin = j == 0 && bv > 0.0 && bv >= rc.x;
+        if (rwin) rwin = bv >= smem_max_pos(&S.rowC[i].x, bv);
+        const unsigned cm = __ballot_sync(FULL, cwin), rm = __ballot_sync(FULL, rwin);
+        if (cm | rm) {
+            if (wcnt + __popc(cm) + __popc(rm) > WCAP) { wins += apply_winners<T>(S, wcnt, prof, lane); wcnt = 0; }
+            if (cwin) { Winner w; w.v = pv; w.slot = c0 + x; w.idx = r0 + i; S.wlist[wcnt + __popc(cm & lt)] = w; }
+            wcnt += __popc(cm);
+            if (rwin) { Winner w; w.v = bv; w.slot = r0 + i; w.idx = c0 + bx; S.wlist[wcnt + __popc(rm & lt)] = w; }
+            wcnt += __popc(rm);
         }
     }
+    if (wcnt) wins += apply_winners<T>(S, wcnt, prof, lane);
     wins = __reduce_add_sync(FULL, wins);
     if (lane == 0) { S.stat[0] += nhits; S.stat[1] += wins; }
     __syncwarp();
@@ -508,11 +532,16 @@ int band_count(int sublen, int excl) {
 // many rows and triples the filter hits at n = 2^18).  Returns the total item count.
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start) {
     const int nb = band_count(sublen, excl);
-    const int nlb = nb > rank ? (nb - rank + world - 1) / world : 0;
+    const int own = nb > rank ? (nb - rank + world - 1) / world : 0;
+    // Every rank walks band 0 first, ranks > 0 redundantly (1 band of ~nb / world): it is the band in which the
+    // column role of a slot (lag 64..576 rows earlier, same CTA) warms the slot's row threshold almost at once, so
+    // the start-up phase in which every cell passes the filter is as short on every rank as it is on rank 0.
+    const int dup = rank > 0 && nb > 0 ? 1 : 0;
+    const int nlb = own + dup;
     item_start.assign(2 * (size_t)nlb + 1, 0);
     long long total = 0;
     for (int lb = 0; lb < nlb; ++lb) {
-        const int band = rank + lb * world;
+        const int band = lb < dup ? 0 : rank + (lb - dup) * world;
         const int nrows = sublen - (excl + band * BAND_W);
         item_start[lb] = (int)total;
         item_start[(size_t)nlb + 1 + lb] = band;

@@ -57,10 +57,11 @@ def compute_merged(plan, corr_buf, index_buf, world, group=None):
     few), then every rank walks the rest of its bands and the profiles are merged again.  Returns the number of
     kernels launched besides the tile kernel."""
     nlb = plan.local_bands()
-    warm = min(nlb, max(1, -(-WARM_BANDS_TOTAL // world)))
+    warm = min(nlb, max(2, -(-WARM_BANDS_TOTAL // world)))
     extra = 0
     if world > 1 and warm < nlb:
-        plan.compute_bands(0, warm)
+        plan.compute_bands(0, 1)            # band 0 on every rank (see build_item_table): warms every slot's threshold
+        plan.compute_bands(1, warm)
         merge_plan_across_ranks(plan, corr_buf, index_buf, group=group)
         plan.compute_bands(warm, -1)
         extra += 3
