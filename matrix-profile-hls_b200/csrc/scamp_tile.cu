@@ -64,7 +64,10 @@ constexpr int COL_SLOTS = DPT * COL_STRIDE;
 constexpr unsigned FULL = 0xffffffffu;
 
 struct __align__(16) Winner { double v; int slot; int idx; };
-constexpr int WCAP = 40;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners)
+#ifndef MPB_WCAP
+#define MPB_WCAP 96
+#endif
+constexpr int WCAP = MPB_WCAP;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners)
 
 template <typename T>
 struct WarpSmem {

@@ -291,3 +291,83 @@ def test_error_behaviour(mp, ctx):
         mp.MatrixProfileKernelTLF(1024, 16, 99, inp, out, w=32)    # iteration out of range
     with pytest.raises(mp.MpbError):
         mp.MatrixProfileKernelTLF(1024, 16, 0, inp, out, w=4)      # w < 8 (row-reduce lanes, Vanilla.cpp:29-36)
+
+
+def test_compute_in_band_pieces_equals_one_launch(mp, ctx):
+    """mpb_plan_compute_bands: walking the bands in three launches gives the profile of the single launch, bit for bit
+    (the phased multi-GPU step relies on it)."""
+    g = load_golden("walk65536_m256_w4096_t128")
+    T, m = g["T"], g["m"]
+    whole = run_plan(mp, ctx, T, m)
+    whole.finalize()
+    MP0, MPI0, corr0 = whole.download()
+    plan = mp.Plan(ctx, T.size, m, mp.F64, 0)
+    plan.upload_series(T)
+    plan.precompute()
+    nlb = plan.local_bands()
+    assert nlb == whole.timings()["bands"] and nlb > 4
+    plan.compute_bands(0, 1)
+    plan.compute_bands(1, 4)
+    plan.compute_bands(4, -1)
+    plan.finalize()
+    MP, MPI, corr = plan.download()
+    assert np.array_equal(corr, corr0) and np.array_equal(MPI, MPI0) and np.array_equal(MP, MP0)
+    with pytest.raises(mp.MpbError):
+        plan.compute_bands(5, 2)
+    plan.close(); whole.close()
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_seed_profile_does_not_change_the_result(mp, ctx, oracle, dtype):
+    """The lag-m/4 seed diagonal is an ordinary diagonal computed twice: with and without it the profile agrees to
+    rounding (the seed's dot product and the chain round differently) and the indices are the same."""
+    g = load_golden("walk65536_m256_w4096_t128")
+    T, m = g["T"], g["m"]
+    out = []
+    for flags in (0, mp.FLAG_NO_SEED):
+        plan = run_plan(mp, ctx, T, m, dtype, flags)
+        plan.finalize()
+        out.append(plan.download())
+        plan.close()
+    tol = 1e-12 if dtype == 0 else 2e-6
+    assert np.abs(out[0][2] - out[1][2]).max() <= tol
+    differ = out[0][1] != out[1][1]
+    assert differ.mean() < 1e-3          # only exact-tie / last-bit cases may pick the other neighbour
+    if dtype == 0:
+        check_profile(oracle, T, m, out[0][2], out[0][1], out[0][0], g["vanilla_corr"], g["vanilla_MPI"])
+
+
+def test_filter_statistics_are_sane(mp, ctx):
+    """The QT-domain block filter must reject almost everything on a converged profile: replayed blocks and parked
+    thread-rows are a small fraction of the work, and every profile improvement went through the exact path."""
+    rng = np.random.default_rng(5)
+    n, m = 1 << 17, 256
+    T = rng.random(n)
+    plan = run_plan(mp, ctx, T, m)
+    plan.finalize()
+    MP, MPI, corr = plan.download()
+    t = plan.timings()
+    plan.close()
+    blocks = t["cells"] / (64 * 32)                     # 8 rows x 8 diagonals x 32 lanes per block
+    assert 0 < t["replays"] < 0.25 * blocks
+    assert t["slow_updates"] >= (MPI >= 0).sum() * 0.5  # at least about one exact update per subsequence
+    assert np.isfinite(MP).all() and corr.min() > 0 and corr.max() <= 1 + 1e-12
+
+
+def test_fast_path_matches_strict_on_tsb_shaped_series(mp, ctx):
+    """n = 2^18 uniform series (the shape of the reference's data/binary/*.tsb): fast path vs MPB_FLAG_STRICT
+    (= the reference kernels' bits) within the 1e-9 budget, indices identical where the values are not tied."""
+    rng = np.random.default_rng(1234)
+    n, m = 1 << 18, 256
+    T = rng.random(n)
+    res = []
+    for flags in (0, mp.FLAG_STRICT):
+        plan = run_plan(mp, ctx, T, m, mp.F64, flags)
+        plan.finalize()
+        res.append(plan.download())
+        plan.close()
+    rel = np.abs(res[0][2] - res[1][2]) / res[1][2]
+    assert rel.max() <= RTOL
+    bad = res[0][1] != res[1][1]
+    assert bad.mean() < 1e-4
+    assert (rel[bad] <= RTOL).all()
