@@ -118,6 +118,10 @@ int mpb_plan_set_shard(mpb_plan *plan, int rank, int world);
 /* Rows per re-seeded segment (multiple of 128; 0 = never re-seed; negative = choose automatically, the default). */
 int mpb_plan_set_segment_rows(mpb_plan *plan, int rows);
 int mpb_plan_segment_rows(mpb_plan *plan);
+/* Local bands covered by the sketch pass that precedes the first tile-kernel launch of a step (0 = off, negative =
+ * default): it walks those bands once without the hit machinery and leaves a lower bound of every slot's best
+ * correlation in the profile, so the filter is tight from the first tile on.  Result-neutral. */
+int mpb_plan_set_sketch_bands(mpb_plan *plan, int bands);
 int mpb_plan_upload_series(mpb_plan *plan, const double *T_host);   /* async H2D of T[n] */
 void *mpb_plan_series_device_ptr(mpb_plan *plan);                   /* double[n] in HBM, caller may fill it */
 int mpb_plan_precompute(mpb_plan *plan);                            /* kernel (1) */

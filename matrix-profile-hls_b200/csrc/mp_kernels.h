@@ -40,6 +40,10 @@ int default_seg_rows(int sublen, int excl, int m, int world, int sm_count);
 cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *mnc, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *mnc, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 
+// sketch pass over the items of `p` (first bands of a step): hint[np] <- high words of per-slot lower bounds, then borrowed entries into prof
+cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+
 // kernel (3): merge.cu
 cudaError_t launch_finalize(const ProfileEntry *prof, int sublen, int m, double *MP, int32_t *MPI, double *corr, cudaStream_t s);
 cudaError_t launch_export(const ProfileEntry *prof, int sublen, double *corr, int32_t *index, cudaStream_t s);

@@ -8,8 +8,14 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
+#include <set>
 #include <vector>
+
+#ifndef MPB_DEFAULT_SKETCH_BANDS
+#define MPB_DEFAULT_SKETCH_BANDS 1
+#endif
 
 namespace mpb {
 int fma_peak_chains();
@@ -61,6 +67,8 @@ struct mpb_plan {
     double *MP = nullptr, *corr = nullptr;
     int32_t *MPI = nullptr;
     unsigned long long *slow_counter = nullptr;
+    int *hint = nullptr;                  // np high words: lower bounds of the slots' best correlation from the sketch pass
+    int sketch_bands = -1;                // local bands the sketch pass covers (-1 = default, 0 = off)
     int seg_rows = -1;                    // requested (-1 = auto)
     int seg_rows_eff = 0;                 // in effect for the current table
     int *item_start = nullptr;            // device prefix table of work items
@@ -72,6 +80,17 @@ struct mpb_plan {
     mpb_timings tm = {};
     bool ran_h2d = false;
 };
+
+// Live-handle registry: destroying a context destroys the plans and buffers created on it first, and destroying a
+// handle twice (or after its context went away) is a no-op -- language bindings finalise objects in any order.
+namespace {
+std::mutex g_reg_mu;
+std::set<mpb_context *> g_ctxs;
+std::set<mpb_plan *> g_plans;
+std::set<mpb_buffer *> g_bufs;
+template <typename H> bool reg_take(std::set<H *> &set, H *h) { std::lock_guard<std::mutex> l(g_reg_mu); return set.erase(h) > 0; }
+template <typename H> void reg_add(std::set<H *> &set, H *h) { std::lock_guard<std::mutex> l(g_reg_mu); set.insert(h); }
+}  // namespace
 
 extern "C" {
 
@@ -110,12 +129,22 @@ int mpb_context_create(int ordinal, mpb_context **out) {
     CU(cudaEventCreate(&c->mark));
     CU(cudaEventCreate(&c->now));
     CU(cudaEventRecord(c->mark, c->stream));
+    reg_add(g_ctxs, c);
     *out = c;
     return MPB_OK;
 }
 
 int mpb_context_destroy(mpb_context *c) {
-    if (!c) return MPB_OK;
+    if (!c || !reg_take(g_ctxs, c)) return MPB_OK;
+    std::vector<mpb_plan *> plans;
+    std::vector<mpb_buffer *> bufs;
+    {
+        std::lock_guard<std::mutex> l(g_reg_mu);
+        for (mpb_plan *p : g_plans) if (p->ctx == c) plans.push_back(p);
+        for (mpb_buffer *b : g_bufs) if (b->ctx == c) bufs.push_back(b);
+    }
+    for (mpb_plan *p : plans) mpb_plan_destroy(p);
+    for (mpb_buffer *b : bufs) mpb_buffer_destroy(b);
     cudaSetDevice(c->device);
     if (c->tlf_scratch) cudaFree(c->tlf_scratch);
     if (c->mark) cudaEventDestroy(c->mark);
@@ -150,12 +179,13 @@ int mpb_buffer_create(mpb_context *c, size_t bytes, mpb_buffer **out) {
     b->bytes = bytes;
     cudaError_t e = cudaMalloc(&b->ptr, bytes ? bytes : 1);
     if (e != cudaSuccess) { delete b; return fail(MPB_E_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); }
+    reg_add(g_bufs, b);
     *out = b;
     return MPB_OK;
 }
 
 int mpb_buffer_destroy(mpb_buffer *b) {
-    if (!b) return MPB_OK;
+    if (!b || !reg_take(g_bufs, b)) return MPB_OK;
     cudaSetDevice(b->ctx->device);
     cudaFree(b->ptr);
     delete b;
@@ -241,10 +271,10 @@ int64_t mpb_useful_cells(int n, int m) {
 }
 
 int mpb_plan_destroy(mpb_plan *p) {
-    if (!p) return MPB_OK;
+    if (!p || !reg_take(g_plans, p)) return MPB_OK;
     cudaSetDevice(p->ctx->device);
     cudaStreamSynchronize(p->ctx->stream);
-    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start};
+    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start, p->hint};
     for (void *q : ptrs) if (q) cudaFree(q);
     for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
     delete p;
@@ -260,6 +290,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     CU(cudaSetDevice(c->device));
     mpb_plan *p = new (std::nothrow) mpb_plan();
     if (!p) return fail(MPB_E_NOMEM, "out of host memory");
+    reg_add(g_plans, p);              // from here on mpb_plan_destroy(p) releases whatever was allocated
     if (flags & MPB_FLAG_STRICT) flags |= MPB_FLAG_SEQ_MEAN | MPB_FLAG_NO_RESEED;
     p->ctx = c; p->n = n; p->m = m; p->dtype = dtype; p->flags = flags;
     p->sublen = n - m + 1; p->excl = m / 4; p->np = mpb::padded_len(p->sublen);
@@ -281,6 +312,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     ALLOC(p->corr, sizeof(double) * (size_t)p->sublen);
     ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
     ALLOC(p->slow_counter, 4 * sizeof(unsigned long long));
+    ALLOC(p->hint, sizeof(int) * np);
 #undef ALLOC
     // zero padding beyond sublen is what lets tiles run off the matrix edge without bounds checks
     CU(cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream));
@@ -308,6 +340,12 @@ int mpb_plan_set_segment_rows(mpb_plan *p, int rows) {
 }
 
 int mpb_plan_segment_rows(mpb_plan *p) { return p ? p->seg_rows_eff : -1; }
+
+int mpb_plan_set_sketch_bands(mpb_plan *p, int bands) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    p->sketch_bands = bands < 0 ? -1 : bands;
+    return MPB_OK;
+}
 
 // (band, segment) work-item table of this rank: rebuilt when the shard or the segment length changes.
 static int plan_build_table(mpb_plan *p) {
@@ -392,6 +430,20 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
         CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
         CU(cudaEventRecord(p->ev[4], s));
         p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
+        // Sketch pass over the first bands of this call (scamp_tile.cu): lower bounds for every slot, so that the tile
+        // kernel meets a tight filter in the bands where the profile would still be empty.  Result-neutral; never in
+        // the chain-faithful modes (their seg_rows = 0 makes a band a single item anyway).
+        int sk = p->sketch_bands < 0 ? MPB_DEFAULT_SKETCH_BANDS : p->sketch_bands;
+        if (p->flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_SEED | MPB_FLAG_NO_RESEED)) sk = 0;
+        if (sk > lb_end) sk = lb_end;
+        if (sk > 0 && p->nlb > 0) {
+            mpb::TileLaunch sl = tl;
+            sl.item_begin = p->table_host[0];
+            sl.items = (long long)p->table_host[sk] - sl.item_begin;
+            if (p->dtype == MPB_F64) CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, s));
+            else CU(mpb::launch_sketch_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->qt0, p->hint, p->prof, sl, s));
+            p->tm.launches += sl.items > 0 ? 2 : 0;
+        }
     }
     if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->mnc, (const double *)p->qt0, p->prof, tl, s));
     else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->mnc, (const float *)p->qt0, p->prof, tl, s));

@@ -67,6 +67,9 @@ struct __align__(16) Winner { double v; int slot; int idx; };
 #ifndef MPB_WCAP
 #define MPB_WCAP 96
 #endif
+#ifndef MPB_STAGE_BATCH
+#define MPB_STAGE_BATCH 1
+#endif
 constexpr int WCAP = MPB_WCAP;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners)
 
 template <typename T>
@@ -441,6 +444,37 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             }
             if (lane % RB == 0 && i < ROWS_STAGED) S.rowK[i / RB] = rb;
         }
+#if MPB_STAGE_BATCH
+        {   // every global load of the column window is issued before the first one is consumed: one L2 round trip per
+            // tile instead of one per unrolled group (the ncu source view of v6 had 20 % of the samples in this staging)
+            constexpr int NCI = (COL_WIN + 31) / 32, NQI = (WarpSmem<T>::NK + 31) / 32;
+            T2 ca[NCI], nv[NCI];
+            double cb[NCI];
+            T mq[NQI];
+#pragma unroll
+            for (int k = 0; k < NCI; ++k) {
+                const int x = min(lane + 32 * k, COL_WIN - 1);
+                ca[k] = df_dg[c0 + x];
+                nv[k] = nm[c0 + x];                         // {norm_c, inv_c}
+                cb[k] = __ldcg(&prof[c0 + x].corr);
+            }
+#pragma unroll
+            for (int k = 0; k < NQI; ++k) { const int q = lane + 32 * k; mq[k] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0)); }
+#pragma unroll
+            for (int k = 0; k < NCI; ++k) {
+                const int x = lane + 32 * k;
+                if (x < COL_WIN) {
+                    const int p = col_slot(x);
+                    S.colA[p] = ca[k];
+                    S.colBest[p] = cb[k];
+                    S.colInv[p] = nv[k].y;
+                    S.ck[p] = nv[k].x < pos_inf(T(0)) ? key_of(mul_rn((T)cb[k], nv[k].x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < NQI; ++k) { const int q = lane + 32 * k; if (q < WarpSmem<T>::NK) S.mncK[q] = mq[k]; }
+        }
+#else
 #pragma unroll 4
         for (int x = lane; x < COL_WIN; x += 32) {
             const int p = col_slot(x);
@@ -452,6 +486,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn((T)cbest, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
         }
         for (int q = lane; q < WarpSmem<T>::NK; q += 32) S.mncK[q] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0));
+#endif
         __syncwarp();
         // minima of the column keys over the MNC_WIN = 15 columns of each block window: lane owns window q
         // (columns DPT*q .. DPT*q + 14 = all of entry q, classes 0..6 of entry q + 1); beyond the staged window: +inf
@@ -522,6 +557,159 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         atomicAdd(counters, (unsigned long long)S.stat[0]); atomicAdd(counters + 1, (unsigned long long)S.stat[1]);
         atomicAdd(counters + 2, (unsigned long long)S.stat[2]);
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sketch pass.  The filter is only as tight as the profile, and in the first bands of a step the profile is empty:
+// nearly every cell of band 0 improves its row or its column, every block is replayed, every row parked and drained
+// (measured: band 0 = 1/2048 of the cells but 6-7 ms of a 156 ms step, and the same 6-7 ms on EVERY rank of a
+// multi-GPU job, where it is a quarter of the rank's time).  The sketch walks the first bands once WITHOUT the
+// hit machinery: the same work items, the same chains (bit-identical QT), P = (QT * inv_r) * inv_c for every cell
+// (the reference's per-cell form, kernel/MatrixProfileKernelVanilla.cpp:84), but only the HIGH WORD of P is kept --
+// a running integer max per column (registers while the column is in the lane's window, then shared memory) and
+// per row (one REDUX.MAX per row) -- and pushed into hint[] with a 32-bit atomic max per row / column and tile.
+// hint[s] is then a lower bound of slot s' best correlation over the sketched bands; apply_hint_kernel stores it,
+// lowered by two high-word ulps, as a "borrowed" entry {bound, index -1} wherever it beats the slot.  The tile
+// kernel then walks the SAME bands with a tight filter: the cell behind each bound passes (P >= bound), is
+// recorded exactly and replaces the borrowed entry (equal corr -> any real index beats -1), so the result is
+// unchanged.  Cost: 4 FP64-pipe ops per sketched cell, no CAS, no replay.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
+sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ qt0,
+              const double *__restrict__ Tser, const double *__restrict__ mu, int *__restrict__ hint,
+              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int seg_rows) {
+    using T2 = typename Tr<T>::T2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
+    int *rowK = reinterpret_cast<int *>(S.wlist);               // [i] high word of the row's best P in this tile
+    static_assert(WCAP * 16 >= ROWS_STAGED * 4, "row maxima alias the winner list");
+
+    int lo = 0, hi = nlb;
+    const int item = blockIdx.x + item_begin;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
+    const int seg = item - item_start[lo];
+    const int band = item_start[nlb + 1 + lo];
+    const int d0w = excl + band * BAND_W + warp * WARP_DIAGS;
+    const int nrows = sublen - d0w;
+    const int rbeg = seg_rows > 0 ? seg * seg_rows : 0;
+    const int rend = seg_rows > 0 ? min(rbeg + seg_rows, nrows) : nrows;
+    if (rbeg >= rend) return;
+
+    T qt[DPT];
+    if (seg == 0) {
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) qt[j] = qt0[d0w + lane * DPT + j];
+    } else {
+        reseed<T>(qt, S, Tser, mu, n, m, sublen, rbeg - 1, d0w, lane);
+    }
+    bool first_tile = true;
+    for (int r0 = rbeg; r0 < rend; r0 += TILE_H) {
+        const int c0 = r0 + d0w;
+        __syncwarp();
+        for (int i = lane; i < ROWS_STAGED; i += 32) {
+            S.rowA[i] = df_dg[r0 + i];
+            S.rowC[i] = make_double2(0.0, (double)nm[r0 + i].y);
+        }
+#pragma unroll 4
+        for (int x = lane; x < COL_WIN; x += 32) {
+            const int p = col_slot(x);
+            S.colA[p] = df_dg[c0 + x];
+            S.colInv[p] = nm[c0 + x].y;
+            S.ck[p] = 0;
+        }
+        __syncwarp();
+        T cdf[DPT], cdg[DPT], civ[DPT];
+        int cmax[DPT];
+#pragma unroll
+        for (int k = 0; k < DPT; ++k) {
+            const T2 a = S.colA[k * COL_STRIDE + lane];
+            cdf[k] = a.x; cdg[k] = a.y;
+            civ[k] = S.colInv[k * COL_STRIDE + lane];
+            cmax[k] = 0;
+        }
+        if (first_tile) {
+            const T2 ra = S.rowA[0];
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) qt[j] = qt_step<false>(qt[j], ra.x, ra.y, cdf[j], cdg[j]);
+            first_tile = false;
+        }
+#pragma unroll 1
+        for (int I = 0; I < TILE_H / DPT; ++I) {
+            const int e0 = I + lane;
+#pragma unroll
+            for (int ii = 0; ii < DPT; ++ii) {
+                const int i = I * DPT + ii;
+                const T ir = (T)S.rowC[i].y;
+                const T2 ra = S.rowA[i + 1];
+                int kp[DPT];
+#pragma unroll
+                for (int j = 0; j < DPT; ++j) {
+                    const int k = (ii + j) % DPT;
+                    kp[j] = __double2hiint((double)corr_of(qt[j], ir, civ[k]));
+                    cmax[k] = max(cmax[k], kp[j]);
+                }
+                const int a = __vimax3_s32(kp[0], kp[1], kp[2]), b = __vimax3_s32(kp[3], kp[4], kp[5]);
+                const int rm = __reduce_max_sync(FULL, __vimax3_s32(kp[6], kp[7], max(a, b)));
+                if (lane == ii) rowK[i] = rm;
+                // the column leaving the lane's window (tile column i + DPT*lane) hands its maximum to shared memory,
+                // the one entering (i + DPT*lane + DPT) takes its register slot
+                const int p = ii * COL_STRIDE + e0;
+                S.ck[p] = max(S.ck[p], cmax[ii]);
+                cmax[ii] = 0;
+                const T2 nd = S.colA[p + 1];
+                cdf[ii] = nd.x; cdg[ii] = nd.y;
+                civ[ii] = S.colInv[p + 1];
+#pragma unroll
+                for (int j = 0; j < DPT; ++j) {
+                    const int k = (ii + 1 + j) % DPT;
+                    qt[j] = qt_step<false>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);
+                }
+            }
+            __syncwarp();      // the next block's lanes update the shared-memory maxima this block's neighbours wrote
+        }
+#pragma unroll
+        for (int k = 0; k < DPT; ++k) {                        // columns still in the windows: TILE_H + DPT*lane + k
+            const int p = k * COL_STRIDE + TILE_H / DPT + lane;
+            S.ck[p] = max(S.ck[p], cmax[k]);
+        }
+        __syncwarp();
+        for (int i = lane; i < TILE_H; i += 32) { const int v = rowK[i]; if (v > 0) atomicMax(hint + r0 + i, v); }
+        for (int x = lane; x < COL_WIN; x += 32) { const int v = S.ck[col_slot(x)]; if (v > 0) atomicMax(hint + c0 + x, v); }
+    }
+}
+
+// hint[i] (high word of a lower bound of slot i's best correlation) -> borrowed profile entry {bound, -1}
+__global__ void apply_hint_kernel(const int *__restrict__ hint, ProfileEntry *__restrict__ prof, int sublen) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sublen) return;
+    const int h = hint[i] - 2;                                  // two high-word ulps (2e-6 relative) below any rounding concern
+    if (h <= 0) return;
+    const double v = __hiloint2double(h, 0);
+    if (v > prof[i].corr) { ProfileEntry e; e.corr = v; e.index = -1; e.pad = 0; prof[i] = e; }
+}
+
+template <typename T>
+static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    using T2 = typename Tr<T>::T2;
+    if (p.items <= 0) return cudaSuccess;
+    const size_t smem = (size_t)cta_smem_bytes<T>();
+    cudaError_t e = cudaFuncSetAttribute(sketch_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(hint, 0, sizeof(int) * (size_t)padded_len(p.sublen), s);
+    if (e != cudaSuccess) return e;
+    sketch_kernel<T><<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), qt0, p.series, p.mu, hint,
+                                                               p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.seg_rows);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    apply_hint_kernel<<<(p.sublen + 255) / 256, 256, 0, s>>>(hint, prof, p.sublen);
+    return cudaGetLastError();
+}
+cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    return launch_sketch_t<double>(df_dg, nm, qt0, hint, prof, p, s);
+}
+cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+    return launch_sketch_t<float>(df_dg, nm, qt0, hint, prof, p, s);
 }
 
 int band_count(int sublen, int excl) {

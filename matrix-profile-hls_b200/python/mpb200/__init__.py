@@ -12,6 +12,7 @@
 There is no CPU fallback: a missing library or device raises.  PyTorch is not imported here; the
 multi-GPU plumbing that needs torch.distributed lives in mpb200.dist.
 """
+import atexit
 import ctypes as C
 import os
 import weakref
@@ -54,7 +55,7 @@ EXPORTS = [
     "mpb_last_error", "mpb_version", "mpb_device_count", "mpb_context_create", "mpb_context_destroy", "mpb_context_finish",
     "mpb_context_stream", "mpb_context_device", "mpb_buffer_create", "mpb_buffer_destroy", "mpb_buffer_copy_from_host",
     "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
-    "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_upload_series",
+    "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
     "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_useful_cells", "mpb_measure_fma_peak",
@@ -99,6 +100,17 @@ def useful_cells(n, m):
     return int(lib().mpb_useful_cells(n, m))
 
 
+_LIVE_CONTEXTS = weakref.WeakSet()
+
+
+@atexit.register
+def _close_all():
+    """Release device state while the interpreter and the CUDA runtime are still intact (object finalisers run in
+    arbitrary order at shutdown; the library also ignores handles that are already gone)."""
+    for ctx in list(_LIVE_CONTEXTS):
+        ctx.close()
+
+
 class Context:
     """Replaces OpenCL::Context (OpenCL.hpp:73-107): one device + one command stream."""
 
@@ -106,6 +118,7 @@ class Context:
         self._h = C.c_void_p()
         self._children = weakref.WeakSet()    # plans / buffers must be destroyed before their context
         _chk(lib().mpb_context_create(C.c_int(ordinal), C.byref(self._h)))
+        _LIVE_CONTEXTS.add(self)
 
     def finish(self):
         """Context::Finish(): returns device nanoseconds since the previous finish()."""
@@ -210,6 +223,10 @@ class Plan:
     def set_segment_rows(self, rows):
         """Rows per re-seeded segment (multiple of 256; 0 = never; -1 = automatic)."""
         _chk(lib().mpb_plan_set_segment_rows(self._h, C.c_int(rows)))
+
+    def set_sketch_bands(self, bands):
+        """Local bands covered by the sketch pass before the first tile launch of a step (0 = off; -1 = default)."""
+        _chk(lib().mpb_plan_set_sketch_bands(self._h, C.c_int(bands)))
 
     @property
     def segment_rows(self):

@@ -17,7 +17,7 @@ T = rng.random(n) if kind == "uniform" else np.cumsum(rng.standard_normal(n))
 ctx = mp.Context(0)
 plans = []
 for r in range(W):
-    p = mp.Plan(ctx, n, m, mp.F64, 0); p.set_shard(r, W); p.upload_series(T); plans.append(p)
+    p = mp.Plan(ctx, n, m, mp.F64, 0); p.set_shard(r, W); p.set_sketch_bands(int(os.environ.get("MPB_SKETCH", "-1"))); p.upload_series(T); plans.append(p)
 nlb = min(p.local_bands() for p in plans)
 
 
@@ -52,8 +52,10 @@ for s in scheds:
     if ref is None: ref = (MP, MPI)
     stats = [p.timings() for p in plans]
     tot = sum(max(ts) for ts in phase_ms)
-    print(json.dumps({"world": W, "n": n, "data": kind, "sched": s, "phases": len(bps), "sum_of_phase_max_ms": round(tot, 3),
+    print(json.dumps({"sketch": int(os.environ.get("MPB_SKETCH", "-1")), "world": W, "n": n, "data": kind, "sched": s, "phases": len(bps), "sum_of_phase_max_ms": round(tot, 3),
                       "sum_of_phase_mean_ms": round(sum(sum(ts) / len(ts) for ts in phase_ms), 3),
                       "phase_max_ms": [round(max(ts), 3) for ts in phase_ms][:12],
                       "replays_rank0": stats[0]["replays"], "replays_max": max(t["replays"] for t in stats),
                       "parked_max": max(t["filter_hits"] for t in stats), "same_result": bool(np.array_equal(MP, ref[0]) and np.array_equal(MPI, ref[1]))}), flush=True)
+for p in plans: p.close()
+ctx.close()

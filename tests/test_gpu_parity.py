@@ -371,3 +371,53 @@ def test_fast_path_matches_strict_on_tsb_shaped_series(mp, ctx):
     bad = res[0][1] != res[1][1]
     assert bad.mean() < 1e-4
     assert (rel[bad] <= RTOL).all()
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("series", ["walk65536_m256_w4096_t128", "unif65536_m256_w4096_t128", "walk8192_m100_w1024_t256"])
+def test_sketch_pass_does_not_change_the_result(mp, ctx, series, dtype):
+    """The sketch pass leaves borrowed lower bounds {bound, index -1} in the profile; the tile kernel walks the same
+    bands, records the cell behind every bound exactly and replaces it.  Whatever number of bands is sketched, the
+    profile is bit-identical to the one computed without the sketch, and no borrowed entry survives."""
+    g = load_golden(series)
+    T, m = g["T"], g["m"]
+    res = []
+    for sk in (0, 1, 3, 1000):
+        plan = mp.Plan(ctx, T.size, m, dtype, 0)
+        plan.set_sketch_bands(sk)
+        plan.upload_series(T)
+        plan.precompute(); plan.compute(); plan.finalize()
+        res.append(plan.download())
+        plan.close()
+    for MP, MPI, corr in res[1:]:
+        assert (MPI >= 0).all()
+        assert np.array_equal(corr, res[0][2]) and np.array_equal(MPI, res[0][1]) and np.array_equal(MP, res[0][0])
+
+
+def test_sketch_pass_in_sharded_phased_compute(mp, ctx):
+    """Band shards with the sketch on, walked in pieces with a merge in between (the multi-GPU step): same profile as
+    one unsharded plan without the sketch."""
+    g = load_golden("unif65536_m256_w4096_t128")
+    T, m = g["T"], g["m"]
+    ref = mp.Plan(ctx, T.size, m, mp.F64, 0)
+    ref.set_sketch_bands(0); ref.upload_series(T); ref.precompute(); ref.compute(); ref.finalize()
+    MP0, MPI0, corr0 = ref.download()
+    ref.close()
+    world = 3
+    plans = []
+    for r in range(world):
+        p = mp.Plan(ctx, T.size, m, mp.F64, 0)
+        p.set_shard(r, world); p.set_sketch_bands(2); p.upload_series(T); p.precompute()
+        p.compute_bands(0, 3)
+        plans.append(p)
+    plans[0].merge_peers(plans[1:])
+    for p in plans[1:]:
+        p.merge_peers([plans[0]])
+    for p in plans:
+        p.compute_bands(3, -1)
+    plans[0].merge_peers(plans[1:])
+    plans[0].finalize()
+    MP, MPI, corr = plans[0].download()
+    for p in plans:
+        p.close()
+    assert np.array_equal(corr, corr0) and np.array_equal(MPI, MPI0) and np.array_equal(MP, MP0)
