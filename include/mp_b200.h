@@ -115,7 +115,7 @@ int mpb_plan_destroy(mpb_plan *plan);
 /* Diagonal-band shard: this plan walks bands b with b % world == rank (the reference's round-robin of
  * chunks over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:101-128). Default (0, 1). */
 int mpb_plan_set_shard(mpb_plan *plan, int rank, int world);
-/* Rows per re-seeded segment (multiple of 128; 0 = never re-seed; negative = choose automatically, the default). */
+/* Rows per re-seeded segment (multiple of the tile height, 192; 0 = never re-seed; negative = choose automatically, the default). */
 int mpb_plan_set_segment_rows(mpb_plan *plan, int rows);
 int mpb_plan_segment_rows(mpb_plan *plan);
 /* Local bands covered by the sketch pass that precedes the first tile-kernel launch of a step (0 = off, negative =

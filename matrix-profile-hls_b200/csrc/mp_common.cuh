@@ -30,7 +30,7 @@ static_assert(sizeof(Aggregate<float>) == 8 && sizeof(InputDataPack<float>) == 1
 #define MPB_DPT 8
 #endif
 #ifndef MPB_TILE_H
-#define MPB_TILE_H 128
+#define MPB_TILE_H 192
 #endif
 #ifndef MPB_WARPS
 #define MPB_WARPS 2

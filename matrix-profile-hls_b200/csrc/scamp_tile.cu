@@ -70,6 +70,20 @@ struct __align__(16) Winner { double v; int slot; int idx; };
 #ifndef MPB_STAGE_BATCH
 #define MPB_STAGE_BATCH 1
 #endif
+#ifndef MPB_PARK_EXACT
+#define MPB_PARK_EXACT 0                        // 1: exact P test before a thread-row is parked (v4..v7)
+#endif
+// Blocks of the hot loop per loop iteration.  With 2 the checkpoint / QT register sets alternate and ptxas drops ~27 of
+// the ~38 loop-carried register copies per block; the fp64 loop is issue-bound (a DFMA costs two issue slots, every
+// other instruction one: scripts/dfma_occupancy_probe.cu), so that is 4 % of the step.  The fp32 loop measured slower
+// unrolled (profiles/r01_v8_variants_unroll_occupancy.jsonl).
+#ifndef MPB_HOT_UNROLL_F64
+#define MPB_HOT_UNROLL_F64 2
+#endif
+#ifndef MPB_HOT_UNROLL_F32
+#define MPB_HOT_UNROLL_F32 1
+#endif
+template <typename T> __host__ __device__ constexpr int hot_unroll() { return sizeof(T) == 8 ? MPB_HOT_UNROLL_F64 : MPB_HOT_UNROLL_F32; }
 constexpr int WCAP = MPB_WCAP;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners)
 
 template <typename T>
@@ -317,7 +331,24 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
         }
         const int a = __vimax3_s32(kp[0], kp[1], kp[2]), b = __vimax3_s32(kp[3], kp[4], kp[5]);
         cand |= __vimax3_s32(kp[6], kp[7], max(a, b)) >= max(__double2hiint(rc.x), 1);
+#if MPB_PARK_EXACT
         if (__any_sync(FULL, cand)) hitcnt = park_row<T>(qc, cand, t, i0, r0, c0, hitcnt, prof);
+#else
+        // Thread-rows that pass the high-word test are parked as they are: the drain repeats the comparison exactly, cell
+        // by cell, and a false candidate needs a P within 2^-20 of the current best (rare), so an exact test here
+        // (park_row: 16 DMUL + 24 DSETP per candidate lane behind a call) only duplicated the drain's work.
+        const unsigned mk = __ballot_sync(FULL, cand);
+        if (mk) {
+            if (cand) {
+                const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
+#pragma unroll
+                for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = qc.v[j];
+                S.hitM[pos] = make_int2(i, i + DPT * lane);
+            }
+            hitcnt += __popc(mk);
+            if (hitcnt > HDRAIN) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }
+        }
+#endif
         if (t + 1 < RB) {
             const T2 ra = S.rowA[i + 1];
             const T2 nd = S.colA[t * COL_STRIDE + e0 + 1];   // column entering the window: i + DPT*lane + DPT
@@ -437,12 +468,17 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
                 rb.y = mul_rn(nv.x, sl);
                 rb.x = mul_rn(best, rb.y);
             }
+            // minima over each block of RB = 8 consecutive rows (8 adjacent lanes), taken on the filter keys: the terms are
+            // positive (or +inf), so their high words order like the values, and a key with the low word dropped is a
+            // slightly smaller threshold term -- conservative.  (A double min is DSETP + SEL + FSEL + NaN fix-up and a
+            // 64-bit shuffle two SHFLs: 75 instructions per 32 rows against 12 here.)
+            int kx = key_of(rb.x), ky = key_of(rb.y);
 #pragma unroll
-            for (int sft = 1; sft < RB; sft <<= 1) {            // minima over each block of RB = 8 consecutive rows (8 adjacent lanes)
-                rb.x = min(rb.x, __shfl_xor_sync(FULL, rb.x, sft));
-                rb.y = min(rb.y, __shfl_xor_sync(FULL, rb.y, sft));
+            for (int sft = 1; sft < RB; sft <<= 1) {
+                kx = min(kx, __shfl_xor_sync(FULL, kx, sft));
+                ky = min(ky, __shfl_xor_sync(FULL, ky, sft));
             }
-            if (lane % RB == 0 && i < ROWS_STAGED) S.rowK[i / RB] = rb;
+            if (lane % RB == 0 && i < ROWS_STAGED) { set_key(rb.x, kx); set_key(rb.y, ky); S.rowK[i / RB] = rb; }
         }
 #if MPB_STAGE_BATCH
         {   // every global load of the column window is issued before the first one is consumed: one L2 round trip per
@@ -468,7 +504,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
                     S.colA[p] = ca[k];
                     S.colBest[p] = cb[k];
                     S.colInv[p] = nv[k].y;
-                    S.ck[p] = nv[k].x < pos_inf(T(0)) ? key_of(mul_rn((T)cb[k], nv[k].x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
+                    S.ck[p] = key_of(nv[k].x) < key_of(pos_inf(T(0))) ? key_of(mul_rn((T)cb[k], nv[k].x)) : key_of(pos_inf(T(0)));   // padding (norm = +inf): never a candidate
                 }
             }
 #pragma unroll
@@ -522,7 +558,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         // operands of sub-step 0, loaded one sub-step ahead like all the others
         T2 ra = S.rowA[1];                                 // {df, dg} of row i + 1
         T2 nd = colA[0];                                   // column entering the lane's window: x = i + DPT*lane + DPT
-#pragma unroll 1
+#pragma unroll hot_unroll<T>()
         for (int I = 0; I < TILE_H / DPT; ++I) {
             QVec<T> qc;                                    // QT at the start of the block (replay checkpoint)
 #pragma unroll
@@ -751,7 +787,7 @@ int default_seg_rows(int sublen, int excl, int m, int world, int sm_count) {
     std::vector<int> tab;
     const long long want = 6LL * 3 * sm_count;            // >= 6 waves of 3 CTAs per SM
     while (seg / 2 >= floor_rows && build_item_table(sublen, excl, 0, world, seg, tab) < want) seg /= 2;
-    return seg;
+    return (seg + TILE_H - 1) / TILE_H * TILE_H;          // whole tiles (a no-op for TILE_H = 128)
 }
 
 template <typename T>
