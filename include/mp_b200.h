@@ -112,18 +112,9 @@ int mpb_compute(mpb_context *ctx, const double *T, int n, int m, int dtype, unsi
 /* Plan form: buffers stay resident in HBM between steps. */
 int mpb_plan_create(mpb_context *ctx, int n, int m, int dtype, unsigned flags, mpb_plan **plan);
 int mpb_plan_destroy(mpb_plan *plan);
-/* Diagonal-band shard: this plan walks every world-th band, starting at band `rank` after the row-sharded first bands
- * (the reference's round-robin of chunks over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:101-128).
- * Default (0, 1). */
+/* Diagonal-band shard: this plan walks bands b with b % world == rank (the reference's round-robin of
+ * chunks over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:101-128). Default (0, 1). */
 int mpb_plan_set_shard(mpb_plan *plan, int rank, int world);
-/* Optional (default 0 = off; negative = default): the first `bands` bands of the problem are not dealt band by band: every
- * rank walks all of them, cut into short segments of `seg_rows` rows (multiple of the tile height; <= 0 = default, 768)
- * of which rank r takes segments r, r + world, ...  They come first in every rank's local band order, so a job
- * walks local bands [0, mpb_plan_row_sharded_bands), merges the profiles, and every rank then meets its own bands
- * with the exact profile of those first bands (threshold discovery happens once per job, not once per rank).
- * The cut -- and so the result -- does not depend on the rank count.  Off in the chain-faithful modes. */
-int mpb_plan_set_row_sharded_bands(mpb_plan *plan, int bands, int seg_rows);
-int mpb_plan_row_sharded_bands(mpb_plan *plan, int *count);
 /* Rows per re-seeded segment (multiple of the tile height, 192; 0 = never re-seed; negative = choose automatically, the default). */
 int mpb_plan_set_segment_rows(mpb_plan *plan, int rows);
 int mpb_plan_segment_rows(mpb_plan *plan);

@@ -26,7 +26,6 @@ cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const fl
 struct TileLaunch {
     int n, m, sublen, excl, rank, world;
     int seg_rows;                       // rows per re-seeded segment (multiple of TILE_H); 0 = one full-length chain per diagonal
-    int rs_bands, rs_seg_rows;          // local bands [0, rs_bands) are row-sharded: segments of rs_seg_rows rows, segment s on rank s % world
     bool strict;                        // un-fused QT update (the reference's rounding sequence)
     const double *series, *mu;          // T[n], mu[sublen] (re-seed operands)
     const int *item_start;              // device: prefix table (nlb + 1 entries) followed by the band ids in visiting order (nlb entries)
@@ -36,8 +35,7 @@ struct TileLaunch {
     unsigned long long *counters;       // device: [0] cells parked, [1] profile slots improved, [2] blocks replayed (may be null)
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
-long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, int rs_bands, int rs_seg_rows, std::vector<int> &item_start);
-int row_sharded_bands(int sublen, int excl, int seg_rows, int rs_bands, int rs_seg_rows);   // local bands the table row-shards
+long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);
 int default_seg_rows(int sublen, int excl, int m, int world, int sm_count);
 cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *mnc, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *mnc, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);

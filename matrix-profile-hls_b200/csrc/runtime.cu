@@ -13,12 +13,6 @@
 #include <set>
 #include <vector>
 
-#ifndef MPB_DEFAULT_RS_BANDS
-#define MPB_DEFAULT_RS_BANDS 0          // first bands of the problem that are row-sharded over the ranks (scamp_tile.cu, build_item_table); measured no gain, off
-#endif
-#ifndef MPB_DEFAULT_RS_SEG_ROWS
-#define MPB_DEFAULT_RS_SEG_ROWS (4 * mpb::TILE_H)
-#endif
 #ifndef MPB_DEFAULT_SKETCH_BANDS
 #define MPB_DEFAULT_SKETCH_BANDS 1
 #endif
@@ -75,8 +69,6 @@ struct mpb_plan {
     unsigned long long *slow_counter = nullptr;
     int *hint = nullptr;                  // np high words: lower bounds of the slots' best correlation from the sketch pass
     int sketch_bands = -1;                // local bands the sketch pass covers (-1 = default, 0 = off)
-    int rs_bands = -1, rs_seg_rows = -1;  // row-sharded first bands and their segment length (-1 = default)
-    int rs_eff = 0, rs_seg_eff = 0;       // in effect for the current table
     int seg_rows = -1;                    // requested (-1 = auto)
     int seg_rows_eff = 0;                 // in effect for the current table
     int *item_start = nullptr;            // device prefix table of work items
@@ -349,24 +341,6 @@ int mpb_plan_set_segment_rows(mpb_plan *p, int rows) {
 
 int mpb_plan_segment_rows(mpb_plan *p) { return p ? p->seg_rows_eff : -1; }
 
-static int plan_build_table(mpb_plan *p);
-
-int mpb_plan_set_row_sharded_bands(mpb_plan *p, int bands, int seg_rows) {
-    if (!p) return fail(MPB_E_INVALID, "plan is null");
-    if (seg_rows > 0 && seg_rows % mpb::TILE_H != 0) return fail(MPB_E_INVALID, "segment rows must be a multiple of %d (got %d)", mpb::TILE_H, seg_rows);
-    p->rs_bands = bands < 0 ? -1 : bands; p->rs_seg_rows = seg_rows > 0 ? seg_rows : -1; p->table_dirty = true;
-    return MPB_OK;
-}
-
-int mpb_plan_row_sharded_bands(mpb_plan *p, int *count) {
-    if (!p || !count) return fail(MPB_E_INVALID, "null argument");
-    CU(cudaSetDevice(p->ctx->device));
-    int rc = plan_build_table(p);
-    if (rc != MPB_OK) return rc;
-    *count = p->rs_eff;
-    return MPB_OK;
-}
-
 int mpb_plan_set_sketch_bands(mpb_plan *p, int bands) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     p->sketch_bands = bands < 0 ? -1 : bands;
@@ -379,9 +353,7 @@ static int plan_build_table(mpb_plan *p) {
     int seg = 0;
     if (!(p->flags & MPB_FLAG_NO_RESEED)) seg = p->seg_rows >= 0 ? p->seg_rows : mpb::default_seg_rows(p->sublen, p->excl, p->m, 8 /* nominal rank count: keeps results independent of the GPU count */, p->ctx->sm_count);
     std::vector<int> tab;
-    const int rsb = p->rs_bands >= 0 ? p->rs_bands : MPB_DEFAULT_RS_BANDS, rss = p->rs_seg_rows > 0 ? p->rs_seg_rows : MPB_DEFAULT_RS_SEG_ROWS;
-    const long long items = mpb::build_item_table(p->sublen, p->excl, p->rank, p->world, seg, rsb, rss, tab);
-    p->rs_eff = mpb::row_sharded_bands(p->sublen, p->excl, seg, rsb, rss); p->rs_seg_eff = p->rs_eff > 0 ? rss : 0;
+    const long long items = mpb::build_item_table(p->sublen, p->excl, p->rank, p->world, seg, tab);
     if (items > 0x7fffffffLL) return fail(MPB_E_INVALID, "%lld work items exceed the grid limit; raise the segment length", items);
     CU(cudaStreamSynchronize(p->ctx->stream));
     if (p->item_start) { cudaFree(p->item_start); p->item_start = nullptr; }
@@ -448,7 +420,6 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
     mpb::TileLaunch tl;
     tl.n = p->n; tl.m = p->m; tl.sublen = p->sublen; tl.excl = p->excl; tl.rank = p->rank; tl.world = p->world;
     tl.seg_rows = p->seg_rows_eff;
-    tl.rs_bands = p->rs_eff; tl.rs_seg_rows = p->rs_seg_eff;
     tl.strict = (p->flags & MPB_FLAG_STRICT) != 0;
     tl.series = p->T; tl.mu = p->mu;
     tl.item_start = p->item_start; tl.nlb = p->nlb;

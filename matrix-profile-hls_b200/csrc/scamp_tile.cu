@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ mnc,
             const T *__restrict__ qt0, const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
             const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
-            int rs_bands, int rs_seg_rows, unsigned long long *counters) {
+            unsigned long long *counters) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
@@ -427,8 +427,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
     int lo = 0, hi = nlb;
     const int item = blockIdx.x + item_begin;
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
-    int seg = item - item_start[lo];
-    if (lo < rs_bands) { seg = seg * world + rank; seg_rows = rs_seg_rows; }   // row-sharded first bands: short segments dealt over the ranks
+    const int seg = item - item_start[lo];
     const int band = item_start[nlb + 1 + lo];                  // band ids follow the prefix table
     const int d0w = excl + band * BAND_W + warp * WARP_DIAGS;   // first (longest) diagonal of this warp
     const int nrows = sublen - d0w;                             // rows of that diagonal
@@ -615,8 +614,7 @@ template <typename T>
 __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ qt0,
               const double *__restrict__ Tser, const double *__restrict__ mu, int *__restrict__ hint,
-              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
-              int rs_bands, int rs_seg_rows) {
+              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int seg_rows) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
@@ -626,8 +624,7 @@ sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>
     int lo = 0, hi = nlb;
     const int item = blockIdx.x + item_begin;
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
-    int seg = item - item_start[lo];
-    if (lo < rs_bands) { seg = seg * world + rank; seg_rows = rs_seg_rows; }
+    const int seg = item - item_start[lo];
     const int band = item_start[nlb + 1 + lo];
     const int d0w = excl + band * BAND_W + warp * WARP_DIAGS;
     const int nrows = sublen - d0w;
@@ -738,8 +735,7 @@ static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, in
     e = cudaMemsetAsync(hint, 0, sizeof(int) * (size_t)padded_len(p.sublen), s);
     if (e != cudaSuccess) return e;
     sketch_kernel<T><<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), qt0, p.series, p.mu, hint,
-                                                               p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows,
-                                                               p.rs_bands, p.rs_seg_rows);
+                                                               p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.seg_rows);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     apply_hint_kernel<<<(p.sublen + 255) / 256, 256, 0, s>>>(hint, prof, p.sublen);
@@ -757,45 +753,27 @@ int band_count(int sublen, int excl) {
     return ndiag <= 0 ? 0 : (ndiag + BAND_W - 1) / BAND_W;
 }
 
-// Work-item table of `rank`.  Entries [0, nlb] are the prefix sums of the items per local band and entries
-// [nlb + 1, 2 nlb] the band ids in visiting order (increasing lag: measured better than a bit-reversed order, which
-// delays the first visit of many rows and triples the filter hits at n = 2^18).  Returns the total item count.
-//
-// Local bands [0, rs): the first `rs_bands` bands of the problem, on EVERY rank, cut into short segments of rs_seg_rows
-// rows that are dealt round-robin over the ranks (segment s belongs to rank s mod world; the kernel maps its item
-// index back with seg * world + rank).  These are the bands in which the profile is still empty and nearly every
-// block is replayed (threshold discovery): row-sharding them means each slot's first thresholds are found once per
-// job instead of once per rank, short segments mean one band already fills the GPU, and after a profile merge
-// (dist.compute_merged) every rank starts its own bands with the exact profile of the first rs_bands bands.
-// Local bands [rs, nlb): this rank's own bands b = rs_bands + rank, + world, ... as (band x seg_rows) items
-// (ceil(rows(b) / seg_rows) each, one when seg_rows == 0).  The cut into segments -- and so every QT value -- does
-// not depend on the rank count.
-long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, int rs_bands, int rs_seg_rows, std::vector<int> &item_start) {
+// Work-item table of `rank`, whose bands are b = rank, rank + world, ...: entries [0, nlb] are the prefix sums of
+// the items per band (ceil(rows(b) / seg_rows), one when seg_rows == 0) and entries [nlb + 1, 2 nlb] the band ids
+// in visiting order (increasing lag: measured better than a bit-reversed order, which delays the first visit of
+// many rows and triples the filter hits at n = 2^18).  Returns the total item count.
+// (Up to v7 every rank walked band 0 first, ranks > 0 redundantly, to warm its thresholds; the sketch pass does that
+// better: 8-way emulation 23.4 -> 18.9 ms without the redundant band.  Dealing the first bands over the ranks by row
+// segments, or cutting them into shorter segments, measured no gain: profiles/r01_v8_phase_probe_*.jsonl.)
+long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start) {
     const int nb = band_count(sublen, excl);
-    const int rs = seg_rows > 0 && rs_seg_rows > 0 ? (rs_bands < nb ? rs_bands : nb) : 0;
-    const int rest = nb - rs;
-    const int own = rest > rank ? (rest - rank + world - 1) / world : 0;
-    const int nlb = rs + own;
+    const int nlb = nb > rank ? (nb - rank + world - 1) / world : 0;
     item_start.assign(2 * (size_t)nlb + 1, 0);
     long long total = 0;
     for (int lb = 0; lb < nlb; ++lb) {
-        const int band = lb < rs ? lb : rs + rank + (lb - rs) * world;
+        const int band = rank + lb * world;
         const int nrows = sublen - (excl + band * BAND_W);
         item_start[lb] = (int)total;
         item_start[(size_t)nlb + 1 + lb] = band;
-        if (lb < rs) {
-            const int nseg = (nrows + rs_seg_rows - 1) / rs_seg_rows;
-            total += nseg > rank ? (nseg - rank + world - 1) / world : 0;
-        } else {
-            total += seg_rows > 0 ? (nrows + seg_rows - 1) / seg_rows : 1;
-        }
+        total += seg_rows > 0 ? (nrows + seg_rows - 1) / seg_rows : 1;
     }
     item_start[nlb] = (int)total;
     return total;
-}
-int row_sharded_bands(int sublen, int excl, int seg_rows, int rs_bands, int rs_seg_rows) {
-    const int nb = band_count(sublen, excl);
-    return seg_rows > 0 && rs_seg_rows > 0 ? (rs_bands < nb ? rs_bands : nb) : 0;
 }
 
 // Default segment length: long enough that the re-seed (m FMAs per diagonal per segment against
@@ -806,7 +784,7 @@ int default_seg_rows(int sublen, int excl, int m, int world, int sm_count) {
     int seg = floor_rows < 4096 ? 4096 : floor_rows;
     std::vector<int> tab;
     const long long want = 6LL * 3 * sm_count;            // >= 6 waves of 3 CTAs per SM
-    while (seg / 2 >= floor_rows && build_item_table(sublen, excl, 0, world, seg, 0, 0, tab) < want) seg /= 2;
+    while (seg / 2 >= floor_rows && build_item_table(sublen, excl, 0, world, seg, tab) < want) seg /= 2;
     return (seg + TILE_H - 1) / TILE_H * TILE_H;          // whole tiles (a no-op for TILE_H = 128)
 }
 
@@ -815,14 +793,12 @@ static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *mnc, con
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
     if (p.seg_rows % TILE_H != 0 || p.seg_rows < 0) return cudaErrorInvalidValue;
-    if (p.rs_bands > 0 && (p.rs_seg_rows <= 0 || p.rs_seg_rows % TILE_H != 0 || p.seg_rows == 0)) return cudaErrorInvalidValue;
     const size_t smem = (size_t)cta_smem_bytes<T>();
     auto kern = p.strict ? tile_kernel<T, true> : tile_kernel<T, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), mnc, qt0, p.series, p.mu,
-                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows,
-                                                       p.rs_bands, p.rs_seg_rows, p.counters);
+                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters);
     return cudaGetLastError();
 }
 

@@ -55,7 +55,7 @@ EXPORTS = [
     "mpb_last_error", "mpb_version", "mpb_device_count", "mpb_context_create", "mpb_context_destroy", "mpb_context_finish",
     "mpb_context_stream", "mpb_context_device", "mpb_buffer_create", "mpb_buffer_destroy", "mpb_buffer_copy_from_host",
     "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
-    "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_set_row_sharded_bands", "mpb_plan_row_sharded_bands", "mpb_plan_upload_series",
+    "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
     "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_useful_cells", "mpb_measure_fma_peak",
@@ -223,15 +223,6 @@ class Plan:
     def set_segment_rows(self, rows):
         """Rows per re-seeded segment (multiple of the tile height, 192; 0 = never; -1 = automatic)."""
         _chk(lib().mpb_plan_set_segment_rows(self._h, C.c_int(rows)))
-
-    def set_row_sharded_bands(self, bands, seg_rows=-1):
-        """First bands of the problem that every rank walks in short row segments dealt over the ranks (-1 = default)."""
-        _chk(lib().mpb_plan_set_row_sharded_bands(self._h, C.c_int(bands), C.c_int(seg_rows)))
-
-    def row_sharded_bands(self):
-        c = C.c_int(0)
-        _chk(lib().mpb_plan_row_sharded_bands(self._h, C.byref(c)))
-        return c.value
 
     def set_sketch_bands(self, bands):
         """Local bands covered by the sketch pass before the first tile launch of a step (0 = off; -1 = default)."""

@@ -51,28 +51,22 @@ def merge_plan_across_ranks(plan, corr_buf, index_buf, group=None):
 WARM_BANDS_TOTAL = 48     # diagonal bands (512 diagonals each) after which the filter thresholds are tight
 
 
-def merge_points(nlb, rs, world):
-    """Local-band indices after which the ranks max-merge their profiles: after the row-sharded first bands (every rank
-    then holds their exact profile) and once more when about WARM_BANDS_TOTAL bands have been walked in total."""
-    pts = []
-    if world > 1 and 0 < rs < nlb:
-        pts.append(rs)
-    warm = max(rs, 0) + max(1, -(-(WARM_BANDS_TOTAL - max(rs, 0)) // world))
-    if world > 1 and warm < nlb and (not pts or warm > pts[-1]):
-        pts.append(warm)
-    return pts
+def merge_points(nlb, world):
+    """Local-band indices after which the ranks max-merge their profiles before the final merge: once, when about
+    WARM_BANDS_TOTAL bands have been walked in total."""
+    warm = max(1, -(-WARM_BANDS_TOTAL // world))
+    return [warm] if world > 1 and warm < nlb else []
 
 
 def compute_merged(plan, corr_buf, index_buf, world, group=None):
-    """The multi-GPU compute step: every rank walks its share of the row-sharded first bands (short row segments dealt
-    over the ranks, mpb_plan_set_row_sharded_bands), the profiles are max-merged, every rank walks its first few own
-    bands, the profiles are merged again (each rank's filter thresholds then come from about WARM_BANDS_TOTAL bands of
-    ALL ranks instead of its own few), then every rank walks the rest of its bands and the profiles are merged a last
-    time.  Returns the number of kernels launched besides the tile kernel."""
+    """The multi-GPU compute step: every rank walks its first few bands, the profiles are max-merged (each rank's
+    filter thresholds then come from about WARM_BANDS_TOTAL bands of ALL ranks instead of its own few), then every
+    rank walks the rest of its bands and the profiles are merged again.  Returns the number of kernels launched
+    besides the tile kernel."""
     nlb = plan.local_bands()
     extra = 0
     lo = 0
-    for pt in merge_points(nlb, plan.row_sharded_bands(), world):
+    for pt in merge_points(nlb, world):
         plan.compute_bands(lo, pt)
         merge_plan_across_ranks(plan, corr_buf, index_buf, group=group)
         extra += 3

@@ -18,7 +18,6 @@ ctx = mp.Context(0)
 plans = []
 for r in range(W):
     p = mp.Plan(ctx, n, m, mp.F64, 0); p.set_shard(r, W); p.set_sketch_bands(int(os.environ.get("MPB_SKETCH", "-1")))
-    if os.environ.get("MPB_RS"): p.set_row_sharded_bands(*[int(x) for x in os.environ["MPB_RS"].split(",")])
     p.upload_series(T); plans.append(p)
 nlb = min(p.local_bands() for p in plans)
 
@@ -26,7 +25,7 @@ nlb = min(p.local_bands() for p in plans)
 def breakpoints(s):
     if s == "auto":                       # the schedule dist.compute_merged uses
         from mpb200.dist import merge_points
-        return merge_points(nlb, plans[0].row_sharded_bands(), W) + [-1]
+        return merge_points(nlb, W) + [-1]
     if s.startswith("geo:"):
         _, first, ratio = s.split(":"); b, out = float(first), []
         while b < nlb: out.append(int(round(b))); b *= float(ratio)
@@ -57,7 +56,7 @@ for s in scheds:
     if ref is None: ref = (MP, MPI)
     stats = [p.timings() for p in plans]
     tot = sum(max(ts) for ts in phase_ms)
-    print(json.dumps({"sketch": int(os.environ.get("MPB_SKETCH", "-1")), "rs": os.environ.get("MPB_RS", "default"), "breakpoints": bps, "world": W, "n": n, "data": kind, "sched": s, "phases": len(bps), "sum_of_phase_max_ms": round(tot, 3),
+    print(json.dumps({"sketch": int(os.environ.get("MPB_SKETCH", "-1")), "breakpoints": bps, "world": W, "n": n, "data": kind, "sched": s, "phases": len(bps), "sum_of_phase_max_ms": round(tot, 3),
                       "sum_of_phase_mean_ms": round(sum(sum(ts) / len(ts) for ts in phase_ms), 3),
                       "phase_max_ms": [round(max(ts), 3) for ts in phase_ms][:12],
                       "replays_rank0": stats[0]["replays"], "replays_max": max(t["replays"] for t in stats),

@@ -8,22 +8,16 @@ from mpb200.dist import merge_points, WARM_BANDS_TOTAL   # noqa: E402
 
 
 def test_single_gpu_never_merges():
-    assert merge_points(2048, 0, 1) == [] and merge_points(2048, 8, 1) == []
+    assert merge_points(2048, 1) == []
 
 
 def test_band_sharded_job_merges_once_when_the_thresholds_are_warm():
     for world in (2, 4, 8):
         nlb = 2048 // world
-        pts = merge_points(nlb, 0, world)
+        pts = merge_points(nlb, world)
         assert pts == [-(-WARM_BANDS_TOTAL // world)]          # WARM_BANDS_TOTAL bands walked in total
         assert 0 < pts[0] < nlb
 
 
-def test_row_sharded_first_bands_add_an_early_merge():
-    pts = merge_points(8 + 255, 8, 8)
-    assert pts[0] == 8 and pts[1] > 8 and pts == sorted(set(pts))
-    assert 8 + (pts[1] - 8) * 8 >= WARM_BANDS_TOTAL
-
-
-def test_tiny_problems_skip_the_early_merges():
-    assert merge_points(1, 0, 8) == [] and merge_points(3, 8, 8) == []
+def test_tiny_problems_skip_the_early_merge():
+    assert merge_points(1, 8) == [] and merge_points(6, 8) == []

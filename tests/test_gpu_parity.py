@@ -191,36 +191,6 @@ def test_band_shards_merge_to_unsharded_result(mp, ctx, world):
         p.close()
 
 
-@pytest.mark.parametrize("world", [2, 8])
-def test_row_sharded_first_bands(mp, ctx, world):
-    """mpb_plan_set_row_sharded_bands: the first bands cut into short row segments dealt over the ranks.  The cut does
-    not depend on the rank count (merged shards == single plan, bit for bit) and the profile stays within the
-    tolerance of the reference's Vanilla kernel."""
-    g = load_golden("walk65536_m256_w4096_t128")
-    T, m = g["T"], g["m"]
-
-    def plan_for(shard):
-        p = mp.Plan(ctx, T.size, m, 0, 0)
-        p.set_shard(*shard)
-        p.set_row_sharded_bands(5, 384)
-        p.upload_series(T); p.precompute(); p.compute()
-        return p
-
-    full = plan_for((0, 1))
-    assert full.row_sharded_bands() == 5
-    full.finalize()
-    MP0, MPI0, corr0 = full.download()
-    assert (np.abs(corr0 - g["vanilla_corr"]) / g["vanilla_corr"]).max() <= RTOL
-    plans = [plan_for((r, world)) for r in range(world)]
-    assert all(p.row_sharded_bands() == 5 for p in plans)
-    plans[0].merge_peers(plans[1:])
-    plans[0].finalize()
-    MP, MPI, corr = plans[0].download()
-    assert np.array_equal(corr, corr0) and np.array_equal(MPI, MPI0) and np.array_equal(MP, MP0)
-    for p in plans + [full]:
-        p.close()
-
-
 def test_export_mask_import_roundtrip(mp, ctx):
     """The NCCL-merge building blocks (export -> [all-reduce] -> mask -> [all-reduce] -> import) on one
     device with torch doing the reductions of two shards."""
