@@ -33,6 +33,7 @@ struct TileLaunch {
     long long items;                    // work items of this launch (= grid size)
     int item_begin;                     // first work item of this launch (index into the prefix table)
     unsigned long long *counters;       // device: [0] cells parked, [1] profile slots improved, [2] blocks replayed (may be null)
+    int sketch_band = -1, sketch_seg_rows = 0;   // sketch launches only: walk this one band in segments of sketch_seg_rows rows (own cut; -1 / 0 = the items of the table)
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);

@@ -13,6 +13,9 @@
 #include <set>
 #include <vector>
 
+#ifndef MPB_SKETCH_SEG_ROWS
+#define MPB_SKETCH_SEG_ROWS (4 * mpb::TILE_H)   // rows per work item of a one-band sketch pass
+#endif
 #ifndef MPB_DEFAULT_SKETCH_BANDS
 #define MPB_DEFAULT_SKETCH_BANDS 1
 #endif
@@ -440,6 +443,13 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
             mpb::TileLaunch sl = tl;
             sl.item_begin = p->table_host[0];
             sl.items = (long long)p->table_host[sk] - sl.item_begin;
+            // one band: cut it finer than the tile kernel does, so that it fills the GPU.  fp64 only: a bound from a chain
+            // with other re-seed points is safe when the chains agree far better than the 2e-6 by which the bounds are
+            // lowered (fp64: ~1e-12); fp32 chains differ by up to 1e-5 and keep the tile kernel's own cut (bit-equal QT).
+            if (sk == 1 && p->dtype == MPB_F64 && p->seg_rows_eff > MPB_SKETCH_SEG_ROWS) {
+                sl.sketch_band = p->table_host[(size_t)p->nlb + 1];
+                sl.sketch_seg_rows = MPB_SKETCH_SEG_ROWS;
+            }
             if (p->dtype == MPB_F64) CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, s));
             else CU(mpb::launch_sketch_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->qt0, p->hint, p->prof, sl, s));
             p->tm.launches += sl.items > 0 ? 2 : 0;

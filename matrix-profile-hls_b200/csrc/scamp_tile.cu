@@ -614,18 +614,21 @@ template <typename T>
 __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ qt0,
               const double *__restrict__ Tser, const double *__restrict__ mu, int *__restrict__ hint,
-              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int seg_rows) {
+              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int seg_rows, int direct_band) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
     int *rowK = reinterpret_cast<int *>(S.wlist);               // [i] high word of the row's best P in this tile
     static_assert(WCAP * 16 >= ROWS_STAGED * 4, "row maxima alias the winner list");
 
+    // direct_band >= 0: one band, cut into this launch's own (shorter) segments, block b = segment b -- the bounds only
+    // have to be true lower bounds, so the sketch need not walk the tile kernel's chains (a re-seeded QT differs from
+    // the running one by rounding, ~1e-13, and the bounds are lowered by 2e-6), and one band then fills the GPU.
     int lo = 0, hi = nlb;
     const int item = blockIdx.x + item_begin;
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
-    const int seg = item - item_start[lo];
-    const int band = item_start[nlb + 1 + lo];
+    if (direct_band < 0) while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
+    const int seg = direct_band >= 0 ? (int)blockIdx.x : item - item_start[lo];
+    const int band = direct_band >= 0 ? direct_band : item_start[nlb + 1 + lo];
     const int d0w = excl + band * BAND_W + warp * WARP_DIAGS;
     const int nrows = sublen - d0w;
     const int rbeg = seg_rows > 0 ? seg * seg_rows : 0;
@@ -734,8 +737,15 @@ static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, in
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(hint, 0, sizeof(int) * (size_t)padded_len(p.sublen), s);
     if (e != cudaSuccess) return e;
-    sketch_kernel<T><<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), qt0, p.series, p.mu, hint,
-                                                               p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.seg_rows);
+    long long grid = p.items;
+    int seg_rows = p.seg_rows;
+    if (p.sketch_band >= 0 && p.sketch_seg_rows > 0) {
+        seg_rows = p.sketch_seg_rows;
+        grid = (p.sublen - (p.excl + p.sketch_band * BAND_W) + seg_rows - 1) / seg_rows;
+    }
+    sketch_kernel<T><<<(unsigned)grid, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), qt0, p.series, p.mu, hint,
+                                                            p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, seg_rows,
+                                                            p.sketch_band >= 0 && p.sketch_seg_rows > 0 ? p.sketch_band : -1);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     apply_hint_kernel<<<(p.sublen + 255) / 256, 256, 0, s>>>(hint, prof, p.sublen);

@@ -46,7 +46,13 @@ def main():
         ("walk8192_m100_w1024_t256", random_walk(8192, 11), 100, 1024, 256, False, ("walk", 11)),
         ("walk65536_m256_w4096_t128", random_walk(65536, 1234), 256, 4096, 128, False, ("walk", 1234)),  # BASELINE.json config 1
         ("unif65536_m256_w4096_t128", uniform_series(65536, 1234), 256, 4096, 128, False, ("uniform", 1234)),
+        ("walk32768_m1024_w4096_t128", random_walk(32768, 21), 1024, 4096, 128, False, ("walk", 21)),     # BASELINE.json config 4's m
+        ("walk20480_m4096_w4096_t128", random_walk(20480, 22), 4096, 4096, 128, False, ("walk", 22)),     # config 5's largest m
+        ("unif20480_m32_w4096_t128", uniform_series(20480, 23), 32, 4096, 128, False, ("uniform", 23)),   # config 5's smallest m
     ]
+    only = set(sys.argv[1:])          # optional: regenerate just the named cases
+    if only:
+        cases = [c for c in cases if c[0] in only]
     for name, T, m, w, t, keep, gen in cases:
         n = T.size
         big = n > 16384
@@ -88,6 +94,8 @@ def main():
     # float: reference float kernels on double precompute cast to float (what the host does,
     # include/host/HostSideComputation.hpp:30-41).  Unpinned upstream (no float tests); recorded
     # so the fp32 engine can be compared with the reference's own float path.
+    if only:
+        return
     orc = Oracle()
     for name, T, m, w, t in [("f32_b1024_m16_w256_t128", T1024, 16, 256, 128), ("f32_walk4096_m64_w256_t128", random_walk(4096, 7), 64, 256, 128)]:
         n = T.size

@@ -31,7 +31,7 @@ int scamp(const double *T, double *MP, int *MPI) {
 }
 }  // namespace
 
-#define NM_LIST(X) X(128, 16) X(1024, 16) X(1024, 30) X(1024, 32) X(2048, 64) X(4096, 64) X(8192, 100) X(16384, 128) X(65536, 256)
+#define NM_LIST(X) X(128, 16) X(1024, 16) X(1024, 30) X(1024, 32) X(2048, 64) X(4096, 64) X(8192, 100) X(16384, 128) X(65536, 256) X(32768, 1024) X(20480, 4096) X(20480, 32)
 
 extern "C" int ref_precompute_f64(int n, int m, const double *T, void *out) {
 #define X(N, M) if (n == N && m == M) return precompute<N, M>(T, out);

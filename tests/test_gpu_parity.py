@@ -11,7 +11,8 @@ pytestmark = pytest.mark.gpu
 KAT = ["small128_m16_w32_t16", "b1024_m16_w32_t16", "b1024_m16_w256_t128", "b1024_m32_w512_t128",
        "b1024_m30_w64_t16", "b16384_m128_w1024_t128"]
 SYN = ["walk4096_m64_w256_t128", "walk8192_m100_w1024_t256"]
-BIG = ["walk65536_m256_w4096_t128", "unif65536_m256_w4096_t128"]
+BIG = ["walk65536_m256_w4096_t128", "unif65536_m256_w4096_t128",
+       "walk32768_m1024_w4096_t128", "walk20480_m4096_w4096_t128", "unif20480_m32_w4096_t128"]   # m of BASELINE.json configs 4 and 5
 RTOL = 1e-9
 
 

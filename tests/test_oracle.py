@@ -12,7 +12,8 @@ from oracle_py import IN_F32, RefShim
 KAT = ["small128_m16_w32_t16", "b1024_m16_w32_t16", "b1024_m16_w256_t128", "b1024_m32_w512_t128",
        "b1024_m30_w64_t16", "b16384_m128_w1024_t128"]
 SYN = ["walk4096_m64_w256_t128", "walk8192_m100_w1024_t256"]
-BIG = ["walk65536_m256_w4096_t128", "unif65536_m256_w4096_t128"]
+BIG = ["walk65536_m256_w4096_t128", "unif65536_m256_w4096_t128",
+       "walk32768_m1024_w4096_t128", "walk20480_m4096_w4096_t128", "unif20480_m32_w4096_t128"]   # m of BASELINE.json configs 4 and 5
 
 
 @pytest.mark.parametrize("name", KAT + SYN)
@@ -63,12 +64,13 @@ def test_reference_scamp_known_answers(oracle, name):
 
 @pytest.mark.parametrize("name", BIG)
 def test_config1_full(oracle, name):
-    """BASELINE.json config 1 (n=65536, m=256) in full, multi-threaded chunks."""
+    """BASELINE.json config 1 (n=65536, m=256) and the m = 32 / 1024 / 4096 cases in full, multi-threaded chunks."""
     g = load_golden(name)
     assert bool(g["tiled_equals_vanilla"])
     MP, MPI, corr, cells = oracle.run(g["T"], g["m"], g["w"], "vanilla", nthreads=os.cpu_count() or 4)
     assert np.array_equal(corr, g["vanilla_corr"]) and np.array_equal(MPI, g["vanilla_MPI"])
-    assert cells == sum((65281 - k * 4096) * 4096 for k in range(16))
+    sublen, w = g["T"].size - g["m"] + 1, g["w"]
+    assert cells == sum((sublen - k * w) * w for k in range((sublen + w - 1) // w))   # processed cells, SURVEY section 8-d
 
 
 @pytest.mark.parametrize("name", ["f32_b1024_m16_w256_t128", "f32_walk4096_m64_w256_t128"])
