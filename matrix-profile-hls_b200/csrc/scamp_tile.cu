@@ -70,9 +70,6 @@ struct __align__(16) Winner { double v; int slot; int idx; };
 #ifndef MPB_STAGE_BATCH
 #define MPB_STAGE_BATCH 1
 #endif
-#ifndef MPB_RUN_AHEAD
-#define MPB_RUN_AHEAD 0                         // 1: streaks of candidate blocks skip the hot-loop pass
-#endif
 #ifndef MPB_PARK_EXACT
 #define MPB_PARK_EXACT 0                        // 1: exact P test before a thread-row is parked (v4..v7)
 #endif
@@ -303,16 +300,14 @@ __device__ __noinline__ int park_row(QVec<T> q, bool cand, int t, int i0, int r0
 // Column operands slide through registers exactly as in the hot loop.  Warp-collective; returns the new hit count.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ int hi_word(const double *p) { return reinterpret_cast<const int *>(p)[1]; }
-constexpr int REPLAY_PARKED = 1 << 20;                       // flag in replay_block's return value (the hit count stays below HCAP)
 
 template <typename T, bool STRICT>
-__device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof, QVec<T> *adv) {
+__device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
     const int e0 = i0 / DPT + lane;                          // i0 is a multiple of DPT: class k of entry e0 is column i0 + DPT*lane + k
     if (lane == 0) S.stat[2] += 1;
-    bool parked = false;                                     // warp-uniform: a thread-row of this block was parked
     T cdf[DPT], cdg[DPT], civ[DPT];
     int ckb[DPT];                                            // high word of the column's best (live view; >= 1 so that P <= 0 never passes)
 #pragma unroll
@@ -344,7 +339,6 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
         // (park_row: 16 DMUL + 24 DSETP per candidate lane behind a call) only duplicated the drain's work.
         const unsigned mk = __ballot_sync(FULL, cand);
         if (mk) {
-            parked = true;
             if (cand) {
                 const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
 #pragma unroll
@@ -355,7 +349,7 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
             if (hitcnt > HDRAIN) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }
         }
 #endif
-        if (t + 1 < RB || adv) {                             // adv: one more step, to the first row of the next block
+        if (t + 1 < RB) {
             const T2 ra = S.rowA[i + 1];
             const T2 nd = S.colA[t * COL_STRIDE + e0 + 1];   // column entering the window: i + DPT*lane + DPT
             cdf[t] = nd.x; cdg[t] = nd.y;
@@ -368,8 +362,7 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
             }
         }
     }
-    if (adv) *adv = qc;
-    return hitcnt | (parked ? REPLAY_PARKED : 0);
+    return hitcnt;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -589,37 +582,8 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             }
             const int ka = key_of(mul_rn(rk.x, cwn));
             const int kb = key_of(mul_rn(rk.y, cww));
-            if (__builtin_expect(__any_sync(FULL, run > __vimin_s32_relu(ka, kb)), 0)) {
-                int rv = replay_block<T, STRICT>(qc, I * DPT, r0, c0, hitcnt, prof, nullptr);
-                hitcnt = rv & (REPLAY_PARKED - 1);
-#if MPB_RUN_AHEAD
-                // Candidates come in streaks (the first bands of a step, smooth series): while the blocks keep parking
-                // thread-rows, the next ones are walked in the per-cell form only -- without the hot-loop pass whose filter
-                // would fail anyway (31 % of a replayed block's issue slots).  replay_block then also takes the step to the
-                // next block's first row and hands the QT values back; the hot loop's operand registers are re-loaded after.
-                if ((rv & REPLAY_PARKED) && I + 1 < TILE_H / DPT) {
-                    QVec<T> io;
-#pragma unroll
-                    for (int j = 0; j < DPT; ++j) io.v[j] = qt[j];
-                    do {
-                        ++I;
-                        rv = replay_block<T, STRICT>(io, I * DPT, r0, c0, hitcnt, prof, &io);
-                        hitcnt = rv & (REPLAY_PARKED - 1);
-                    } while ((rv & REPLAY_PARKED) && I + 1 < TILE_H / DPT);
-#pragma unroll
-                    for (int j = 0; j < DPT; ++j) qt[j] = io.v[j];
-                    rowA = S.rowA + 2 + I * DPT;               // the end-of-body increments move both on to block I + 1
-                    colA = S.colA + lane + 1 + I;
-#pragma unroll
-                    for (int k = 0; k < DPT; ++k) {
-                        const T2 a = S.colA[k * COL_STRIDE + lane + I + 1];
-                        cdf[k] = a.x; cdg[k] = a.y;
-                    }
-                    ra = S.rowA[(I + 1) * DPT + 1];
-                    nd = colA[1];
-                }
-#endif
-            }
+            if (__builtin_expect(__any_sync(FULL, run > __vimin_s32_relu(ka, kb)), 0))
+                hitcnt = replay_block<T, STRICT>(qc, I * DPT, r0, c0, hitcnt, prof);
             rowA += DPT; colA += 1;
         }
         if (hitcnt > 0) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }   // candidates never outlive their tile
