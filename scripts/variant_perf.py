@@ -17,6 +17,7 @@ for n in sizes:
             rng = np.random.default_rng(1234)
             T = rng.random(n) if kind == "uniform" else np.cumsum(rng.standard_normal(n))
             plan = mp.Plan(ctx, n, 256, dt, 0)
+            if os.environ.get("MPB_SEG"): plan.set_segment_rows(int(os.environ["MPB_SEG"]))
             plan.upload_series(T)
             best = None
             for rep in range(3):
