@@ -19,6 +19,7 @@ plans = []
 for r in range(W):
     p = mp.Plan(ctx, n, m, mp.F64, 0); p.set_shard(r, W); p.set_sketch_bands(int(os.environ.get("MPB_SKETCH", "-1")))
     p.upload_series(T); plans.append(p)
+    if os.environ.get("MPB_SEG"): p.set_segment_rows(int(os.environ["MPB_SEG"]))
 nlb = min(p.local_bands() for p in plans)
 
 
