@@ -32,13 +32,21 @@ extern "C" {
 #define MPB_F64 0
 #define MPB_F32 1
 
-/* mpb_plan flags.  Default (0) is the fast path: exact window means, nested-FMA QT update, and an exact
- * fp64 re-seed of every diagonal each `segment rows` rows (bounds drift; BASELINE.json north_star). */
+/* mpb_plan flags.  Default (0):
+ *   fp64 -- chain-faithful AND parallel: mu by the reference's running-mean recurrence (HostSideComputation.hpp:23,29),
+ *           nested-FMA QT update, the matrix cut into independent (band x row segment) work items that start from
+ *           exact dot products, and the reference's unbroken single-seed chain (Vanilla.cpp:43-55,81) recovered
+ *           from them by telescoping ("chain carry", csrc/mp_common.cuh): ~1e-12 from the reference's bits.
+ *   fp32 -- exact window means, nested FMA, exact fp64 re-seed of every diagonal each `segment rows` rows, which is
+ *           what bounds the float chain's drift (BASELINE.json north_star). */
 #define MPB_FLAG_STRICT 1u     /* chain-faithful: implies SEQ_MEAN | NO_RESEED and the un-fused QT update (mul,mul,add,add):
                                   bit-identical to the reference kernels' chain, 6 instead of 4 FP64 ops per cell */
 #define MPB_FLAG_SEQ_MEAN 2u   /* mu by the reference's sequential running-mean recurrence (HostSideComputation.hpp:29) */
 #define MPB_FLAG_NO_RESEED 4u  /* one full-length chain per diagonal, seeded at row 0 only (Vanilla.cpp:43-55) */
 #define MPB_FLAG_NO_SEED 8u    /* do not pre-load the profile with the lag-m/4 diagonal (measurement aid; results are the same) */
+#define MPB_FLAG_NO_CHAIN_CARRY 16u /* fp64: keep the re-seeded segments' own values (round 1's fast mode: drifts from the
+                                  reference by up to 6e-9 on a 2^20-sample random walk) */
+#define MPB_FLAG_WINDOW_MEAN 32u /* fp64: exact window means instead of the reference's running mean (no sequential scan) */
 
 typedef struct mpb_context mpb_context; /* replaces OpenCL::Context   (OpenCL.hpp:73-107, 294-317) */
 typedef struct mpb_buffer mpb_buffer;   /* replaces OpenCL::Buffer<T> (OpenCL.hpp:109-211) */
@@ -101,6 +109,11 @@ typedef struct {
     int32_t segment_rows; /* rows per re-seeded segment (0 = full-length chains) */
     int64_t filter_hits;  /* cells that passed the QT-domain filter and were checked exactly against the profile */
     int64_t replays;      /* 8-row x 8-diagonal x 32-lane blocks walked a second time because a cell in them passed the block filter */
+    int64_t chain_candidates;    /* chain-carry mode: values (slot entries + logged near ties) resolved with their carry */
+    double chain_max_correction; /* chain-carry mode: largest relative correction |carry * inv_r * inv_c| / P applied (how far the
+                                    independent segments were from the unbroken chain); 0 in the other modes */
+    double chain_bound;          /* chain-carry mode: upper bound of the ABSOLUTE correction any cell's P could receive */
+    double chain_margin;         /* chain-carry mode: the near-tie margin in effect (relative) */
 } mpb_timings;
 
 /* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised
@@ -140,6 +153,15 @@ int mpb_plan_export(mpb_plan *plan, void *corr_out_dev, void *index_out_dev);
  * so that a min-reduction of index_dev picks the smallest index among the ranks holding the maximum. */
 int mpb_plan_mask_index(mpb_plan *plan, const void *corr_max_dev, void *index_dev);
 int mpb_plan_import(mpb_plan *plan, const void *corr_dev, const void *index_dev);
+/* Chain-carry mode keeps two profiles: the running bests that drive the filter (thresholds) and the result built from
+ * the resolved candidates.  export / mask_index / import / merge_peers address the result (thresholds == 0, default)
+ * or the thresholds (thresholds != 0: the early merge of a multi-GPU step). No effect in the other modes. */
+int mpb_plan_merge_select(mpb_plan *plan, int thresholds);
+/* Near-tie margin of the chain-carry mode: 2^-log2_inverse relative (8..21, default 18).  Candidates within the margin of a
+ * slot's best are deferred to the resolve step; the margin must exceed the corrections (mpb_timings.chain_max_correction). */
+int mpb_plan_set_chain_margin(mpb_plan *plan, int log2_inverse);
+/* Total capacity of the chain-carry near-tie log in entries of 16 bytes (<= 0: automatic, 16 per subsequence). */
+int mpb_plan_set_log_entries(mpb_plan *plan, int64_t entries);
 /* In-library merge over NVLink peer memory (single process, several devices): folds the profiles of
  * `others` into `plan` with an exact (corr, index) max; peers are read through P2P loads. */
 int mpb_plan_merge_peers(mpb_plan *plan, mpb_plan *const *others, int count);

@@ -54,6 +54,43 @@ constexpr int PAD = BAND_W + 4 * TILE_H + 64;
 
 __host__ __device__ inline int padded_len(int sublen) { return ((sublen + PAD + 63) / 64) * 64; }
 
+// ---------------------------------------------------------------------------------------------
+// Telescoped chain carry (fp64 default mode).  The reference seeds every diagonal ONCE at row 0 and walks it to the
+// end (kernel/MatrixProfileKernelVanilla.cpp:43-55,81); its QT at row r is QT_0 + the sum of all updates up to r,
+// drift of the running mean included.  The tile kernel cuts each band into independent row segments that start from
+// an exact dot product S_k (so that thousands of work items run at once).  Because the update is ADDITIVE, the value
+// the reference's chain holds anywhere inside segment k is
+//     C(r, d) = Q'_k(r, d) + D_k(d),     D_0 = 0,   D_{k+1}(d) = D_k(d) + E_k(d) - S_{k+1}(d),
+// where Q'_k is the segment's own chain, E_k its value at the first row of segment k+1 and S_{k+1} the value segment
+// k+1 started from at that same row: the carry of the unbroken chain, recovered by telescoping AFTER the fact.
+// Every work item stores S_k and E_k for its diagonals and a scan over k gives D_k.  While the tile kernel runs, the
+// profile holds the segments' own values P' = Q' * inv_r * inv_c; they differ from the chain's P by a relative
+// delta = D / Q' (1e-8 typically, 1e-6 where a window of the series is nearly flat).  Decisions that a correction of
+// that size could reverse are deferred: a candidate that beats a slot's best by more than the MARGIN replaces it for
+// good, one that loses by more than the margin is dropped for good, and a candidate within the margin of the best goes
+// (or sends the entry it replaces) to a log of near ties.  After the scan the resolve kernel gives every surviving slot
+// entry and every logged near tie its carry, P = P' + D * inv_r * inv_c, and takes the exact (corr, index) max.
+// The filter thresholds are lowered by the margin, so every cell within the margin of a slot's best gets that far.
+// ---------------------------------------------------------------------------------------------
+struct __align__(16) ChainLogEntry { double corr; int32_t slot; int32_t index; };   // P' of cell (slot, index) for slot `slot`
+constexpr int LOG_SHARDS = 64;                       // sub-logs, one append counter each (no single hot address)
+struct ChainFix {
+    double *seg_seed;                // [item - item_base][BAND_W]  S_k (k >= 1), overwritten by D_k in the scan
+    double *seg_end;                 // [item - item_base][BAND_W]  E_k
+    ChainLogEntry *log;              // LOG_SHARDS x shard_cap entries
+    unsigned long long *log_count;   // [LOG_SHARDS * 16] (one counter per 128-byte line); may exceed shard_cap: overflow
+    unsigned int shard_cap;
+    int item_base;                   // first work item of the launch chunk the arrays are laid out for
+    double margin;                   // near-tie margin mu: two values are a near tie when they differ by <= mu * max(value, CHAIN_FLOOR)
+    int key_margin;                  // mu in ulps of a double's high word (one ulp is >= 2^-21 relative), rounded up
+};
+// The margin is relative for correlations above CHAIN_FLOOR and absolute (mu * CHAIN_FLOOR) below it, so that ONE bound
+// on the absolute correction any cell can receive (chain_scan_kernel, mpb_timings.chain_bound) proves it sufficient:
+// 2 * bound <= mu * CHAIN_FLOOR  ==>  no pair of candidates further apart than the margin can change order.
+#define MPB_CHAIN_FLOOR 0.015625
+__host__ __device__ inline double chain_lower(double v, double mu) { return v - mu * (v > MPB_CHAIN_FLOOR ? v : MPB_CHAIN_FLOOR); }   // v minus the margin
+
+
 // Exact (corr, index) max into a global profile slot: larger corr wins, equal corr -> smaller index
 // (deterministic whatever the arrival order / GPU count).  Returns the slot's corr after the update
 // (the band kernel derives its filter threshold from it).
@@ -75,5 +112,6 @@ __device__ __forceinline__ double profile_update(ProfileEntry *slot, double v, i
     }
     return __longlong_as_double((long long)clo);
 }
+
 
 }  // namespace mpb

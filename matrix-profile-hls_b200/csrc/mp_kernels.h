@@ -1,11 +1,11 @@
 // mp_kernels.h -- host-side launchers of the engine's kernels (internal to libmpb200.so).
 #pragma once
+#include "mp_common.cuh"
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <vector>
 
 namespace mpb {
-struct ProfileEntry;
 
 // kernel (1): precompute.cu
 cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream_t s);      // the reference's sequential running mean
@@ -16,9 +16,10 @@ cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, fl
 cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, double *mnc, cudaStream_t s);
 cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, float *mnc, cudaStream_t s);
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s);
-// seeds every profile slot with the cell at lag `lag` (the first diagonal outside the exclusion zone), computed directly
-cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s);
-cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s);
+// seeds every profile slot with the cell at lag `lag` (the first diagonal outside the exclusion zone), computed directly;
+// borrow > 0: as a borrowed lower bound {P * borrow, index -1} instead of the cell itself (chain-carry mode)
+cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s);
+cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s);
 cudaError_t launch_pack_input_f64(const double *df_dg, const double *inv, const double *qt0, int sublen, void *out, cudaStream_t s);
 cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const float *qt0, int sublen, void *out, cudaStream_t s);
 
@@ -34,12 +35,20 @@ struct TileLaunch {
     int item_begin;                     // first work item of this launch (index into the prefix table)
     unsigned long long *counters;       // device: [0] cells parked, [1] profile slots improved, [2] blocks replayed (may be null)
     int sketch_band = -1, sketch_seg_rows = 0;   // sketch launches only: walk this one band in segments of sketch_seg_rows rows (own cut; -1 / 0 = the items of the table)
+    ChainFix chain = {};                // chain-carry mode (fp64, re-seeded segments): log != nullptr switches it on
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);
 int default_seg_rows(int sublen, int excl, int m, int world, int sm_count);
 cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *mnc, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *mnc, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+
+// chain-carry steps 2 and 3 for the local bands [lb_begin, lb_end) of the launch chunk p.chain was laid out for: carry scan, then the
+// surviving threshold entries of `prof` and the logged near ties into `fin`.  imax = launch_inv_block_max's output.
+// stats: [0] largest relative correction applied (double bits) [1] += values resolved [2] |= log overflow [3] bound of any correction
+cudaError_t launch_inv_block_max(const double *inv, int sublen, int seg_rows, double *imax, cudaStream_t s);
+cudaError_t launch_chain_resolve(const TileLaunch &p, int lb_begin, int lb_end, const double *inv, const double *imax, const ProfileEntry *prof, ProfileEntry *fin,
+                                 unsigned long long *stats, cudaStream_t s);
 
 // sketch pass over the items of `p` (first bands of a step): hint[np] <- high words of per-slot lower bounds, then borrowed entries into prof
 cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);

@@ -19,8 +19,8 @@ constexpr int SCAN_THREADS = 256;
 
 __global__ void __launch_bounds__(SCAN_THREADS, 1)
 mu_scan_kernel(const double *__restrict__ T, int n, int m, double *__restrict__ mu) {
-    __shared__ double delta[2][SCAN_CHUNK];
-    __shared__ double out[2][SCAN_CHUNK];
+    __shared__ __align__(16) double delta[2][SCAN_CHUNK];
+    __shared__ __align__(16) double out[2][SCAN_CHUNK];
     __shared__ double carry;
     const int sublen = n - m + 1;
     const int tid = threadIdx.x;
@@ -45,11 +45,28 @@ mu_scan_kernel(const double *__restrict__ T, int n, int m, double *__restrict__ 
     for (int c = 0; c < nchunks; ++c) {
         const int buf = c & 1;
         if (tid == 0) {
+            // the chain itself: 16 increments in registers (LDS.128 one group ahead), 16 dependent DADDs, results back
+            // through STS.128 -- the chain only ever waits for the previous DADD
             double mean = carry;
-#pragma unroll 8
-            for (int e = 0; e < SCAN_CHUNK; ++e) {
-                mean = __dadd_rn(mean, delta[buf][e]);
-                out[buf][e] = mean;
+            const double2 *din = reinterpret_cast<const double2 *>(delta[buf]);
+            double2 *dout = reinterpret_cast<double2 *>(out[buf]);
+            double2 d[8], nd[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) d[k] = din[k];
+#pragma unroll 1
+            for (int e = 0; e < SCAN_CHUNK / 2; e += 8) {
+                const int en = e + 8 < SCAN_CHUNK / 2 ? e + 8 : e;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) nd[k] = din[en + k];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    double2 o;
+                    mean = __dadd_rn(mean, d[k].x); o.x = mean;
+                    mean = __dadd_rn(mean, d[k].y); o.y = mean;
+                    dout[e + k] = o;
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] = nd[k];
             }
             carry = mean;
         } else if (tid >= 32) {                  // warps 1.. prefetch the next chunk and drain the previous one
@@ -176,7 +193,7 @@ __global__ void norm_kernel(const OutT *__restrict__ inv, int sublen, int np, Ou
 template <typename OutT>
 __global__ void __launch_bounds__(STATS_THREADS)
 seed_profile_kernel(const double *__restrict__ T, const double *__restrict__ mu, const OutT *__restrict__ inv, int n, int m, int lag,
-                    ProfileEntry *prof) {
+                    ProfileEntry *prof, double borrow) {
     extern __shared__ double sm[];                   // T[i0 .. i0 + STATS_THREADS + m + lag)
     const int sublen = n - m + 1;
     const int i0 = blockIdx.x * STATS_THREADS;
@@ -196,8 +213,13 @@ seed_profile_kernel(const double *__restrict__ T, const double *__restrict__ mu,
     const OutT qt = (OutT)(q0 + q1);
     const double p = (double)((qt * inv[i]) * inv[j]);
     if (p > 0.0) {
-        profile_update(prof + i, p, j);
-        profile_update(prof + j, p, i);
+        if (borrow > 0.0) {     // chain-carry mode (borrow = the near-tie margin): a lower bound, four margins below the cell; the
+            const double lb = chain_lower(p, 4.0 * borrow);                        // tile kernel meets the cell itself and replaces it
+            if (lb > 0.0) { profile_update(prof + i, lb, -1); profile_update(prof + j, lb, -1); }
+        } else {
+            profile_update(prof + i, p, j);
+            profile_update(prof + j, p, i);
+        }
     }
 }
 
@@ -256,7 +278,7 @@ cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, flo
     return cudaGetLastError();
 }
 template <typename OutT>
-static cudaError_t launch_seed_t(const double *T, const double *mu, const OutT *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s) {
+static cudaError_t launch_seed_t(const double *T, const double *mu, const OutT *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s) {
     const int sublen = n - m + 1;
     if (sublen - lag <= 0) return cudaSuccess;
     const size_t smem = sizeof(double) * (size_t)(STATS_THREADS + m + lag);
@@ -264,14 +286,14 @@ static cudaError_t launch_seed_t(const double *T, const double *mu, const OutT *
         cudaError_t e = cudaFuncSetAttribute(seed_profile_kernel<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    seed_profile_kernel<OutT><<<(sublen - lag + STATS_THREADS - 1) / STATS_THREADS, STATS_THREADS, smem, s>>>(T, mu, inv, n, m, lag, prof);
+    seed_profile_kernel<OutT><<<(sublen - lag + STATS_THREADS - 1) / STATS_THREADS, STATS_THREADS, smem, s>>>(T, mu, inv, n, m, lag, prof, borrow);
     return cudaGetLastError();
 }
-cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s) {
-    return launch_seed_t<double>(T, mu, inv, n, m, lag, prof, s);
+cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s) {
+    return launch_seed_t<double>(T, mu, inv, n, m, lag, prof, borrow, s);
 }
-cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, cudaStream_t s) {
-    return launch_seed_t<float>(T, mu, inv, n, m, lag, prof, s);
+cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s) {
+    return launch_seed_t<float>(T, mu, inv, n, m, lag, prof, borrow, s);
 }
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s) {
     profile_init_kernel<<<(count + 255) / 256, 256, 0, s>>>(prof, count);

@@ -5,6 +5,8 @@
 #include "mp_common.cuh"
 #include "mp_kernels.h"
 
+#include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -18,6 +20,12 @@
 #endif
 #ifndef MPB_DEFAULT_SKETCH_BANDS
 #define MPB_DEFAULT_SKETCH_BANDS 1
+#endif
+#ifndef MPB_CHAIN_MARGIN_LOG2
+#define MPB_CHAIN_MARGIN_LOG2 0                  // near-tie margin of the chain-carry mode = 2^-k; 0 = by series length (default_margin_log2)
+#endif
+#ifndef MPB_CHAIN_CHUNK_ITEMS
+#define MPB_CHAIN_CHUNK_ITEMS (1 << 19)          // work items per launch chunk of the chain-carry mode (4 KB of S_k + 4 KB of E_k each)
 #endif
 
 namespace mpb {
@@ -66,7 +74,20 @@ struct mpb_plan {
     double *T = nullptr, *mu = nullptr;
     void *df_dg = nullptr, *inv = nullptr, *qt0 = nullptr;    // data_t arrays, zero-padded to np
     void *nm = nullptr, *mnc = nullptr;                       // data_t {norm, inv} pairs and window-min norms, np entries
-    mpb::ProfileEntry *prof = nullptr;                        // np slots
+    mpb::ProfileEntry *prof = nullptr;                        // np slots: running bests = the tile kernel's filter thresholds
+    mpb::ProfileEntry *fin = nullptr;                         // np slots: the result profile of the chain-carry mode (else unused; the result is prof)
+    bool seq_mean = false, chain_fix = false;                 // mu by the reference's running recurrence; telescoped chain carry (mp_common.cuh)
+    bool merge_thresholds = false;                            // export / import / merge_peers address prof even in the chain-carry mode
+    double *seg_seed = nullptr, *seg_end = nullptr;           // chain carry: S_k / E_k of the work items of one launch chunk, [chunk_items][BAND_W]
+    long long chunk_items = 0;                                // capacity of those arrays in work items
+    mpb::ChainLogEntry *chain_log = nullptr;                  // LOG_SHARDS sub-logs of log_shard_cap candidates
+    unsigned long long *log_count = nullptr;                  // LOG_SHARDS counters, one per 128-byte line
+    unsigned long long *chain_stats = nullptr;                // [0] largest relative correction (double bits) [1] candidates resolved [2] log overflow seen
+    unsigned log_shard_cap = 0;
+    long long log_entries_req = -1;                           // requested total log capacity (-1 = automatic)
+    double *inv_blockmax = nullptr;                           // largest inv per block of seg_rows rows (bound of the chain-carry corrections)
+    int inv_blocks = 0;
+    int margin_log2 = 17;                                     // near-tie margin = 2^-margin_log2
     double *MP = nullptr, *corr = nullptr;
     int32_t *MPI = nullptr;
     unsigned long long *slow_counter = nullptr;
@@ -277,7 +298,8 @@ int mpb_plan_destroy(mpb_plan *p) {
     if (!p || !reg_take(g_plans, p)) return MPB_OK;
     cudaSetDevice(p->ctx->device);
     cudaStreamSynchronize(p->ctx->stream);
-    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start, p->hint};
+    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start, p->hint,
+                    p->fin, p->seg_seed, p->seg_end, p->chain_log, p->log_count, p->chain_stats, p->inv_blockmax};
     for (void *q : ptrs) if (q) cudaFree(q);
     for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
     delete p;
@@ -296,6 +318,14 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     reg_add(g_plans, p);              // from here on mpb_plan_destroy(p) releases whatever was allocated
     if (flags & MPB_FLAG_STRICT) flags |= MPB_FLAG_SEQ_MEAN | MPB_FLAG_NO_RESEED;
     p->ctx = c; p->n = n; p->m = m; p->dtype = dtype; p->flags = flags;
+    // fp64 default: the reference's running mean and its unbroken single-seed chain (recovered by telescoping over the
+    // re-seeded segments); fp32 default: exact window means and plain re-seeding, which is what bounds ITS drift
+    p->seq_mean = (flags & MPB_FLAG_SEQ_MEAN) || (dtype == MPB_F64 && !(flags & MPB_FLAG_WINDOW_MEAN));
+    p->chain_fix = dtype == MPB_F64 && !(flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_RESEED | MPB_FLAG_NO_CHAIN_CARRY));
+    // The corrections grow with the series length (measured bound, random walk, m = 256: 4e-11 / 7e-10 / 9e-9 / 6e-8 at
+    // n = 2^16 / 2^18 / 2^20 / 2^22) and the margin must be 128 x the bound (chain_check); a wide margin only costs log
+    // entries on very smooth series (m in the thousands), so it is not simply set to the largest value.
+    p->margin_log2 = MPB_CHAIN_MARGIN_LOG2 ? MPB_CHAIN_MARGIN_LOG2 : (n <= (1 << 20) ? 17 : n <= (1 << 22) ? 15 : n <= (1 << 24) ? 13 : 11);
     p->sublen = n - m + 1; p->excl = m / 4; p->np = mpb::padded_len(p->sublen);
     const size_t es = dtype == MPB_F64 ? 8 : 4, np = (size_t)p->np;
 #define ALLOC(ptr, bytes)                                                                            \
@@ -316,12 +346,18 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
     ALLOC(p->slow_counter, 4 * sizeof(unsigned long long));
     ALLOC(p->hint, sizeof(int) * np);
+    if (p->chain_fix) {
+        ALLOC(p->fin, sizeof(mpb::ProfileEntry) * np);
+        ALLOC(p->log_count, sizeof(unsigned long long) * 16 * mpb::LOG_SHARDS);
+        ALLOC(p->chain_stats, 4 * sizeof(unsigned long long));
+    }
 #undef ALLOC
     // zero padding beyond sublen is what lets tiles run off the matrix edge without bounds checks
     CU(cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream));
     CU(cudaMemsetAsync(p->inv, 0, es * np, c->stream));
     CU(cudaMemsetAsync(p->qt0, 0, es * np, c->stream));
     CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), c->stream));
+    if (p->chain_fix) CU(cudaMemsetAsync(p->chain_stats, 0, 4 * sizeof(unsigned long long), c->stream));
     for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
     p->tm.cells = mpb_useful_cells(n, m);
     *out = p;
@@ -364,6 +400,39 @@ static int plan_build_table(mpb_plan *p) {
     CU(cudaMemcpy(p->item_start, tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice));
     p->table_host = tab;
     p->nlb = ((int)tab.size() - 1) / 2; p->items = items; p->seg_rows_eff = seg; p->table_dirty = false;
+    if (p->chain_fix && seg == 0) p->chain_fix = false;          // segment length forced to 0: full-length chains, nothing to carry
+    if (p->chain_fix) {
+        // S_k / E_k arrays: one launch chunk at a time (whole bands; at least the longest band), at most MPB_CHAIN_CHUNK_ITEMS items
+        long long longest = 0;
+        for (int lb = 0; lb < p->nlb; ++lb) longest = std::max(longest, (long long)tab[lb + 1] - tab[lb]);
+        const long long want = std::max(longest, std::min(items, (long long)MPB_CHAIN_CHUNK_ITEMS));
+        if (want > p->chunk_items) {
+            if (p->seg_seed) cudaFree(p->seg_seed);
+            if (p->seg_end) cudaFree(p->seg_end);
+            p->seg_seed = p->seg_end = nullptr; p->chunk_items = 0;
+            const size_t bytes = sizeof(double) * (size_t)want * mpb::BAND_W;
+            if (cudaMalloc((void **)&p->seg_seed, bytes) != cudaSuccess || cudaMalloc((void **)&p->seg_end, bytes) != cudaSuccess) {
+                cudaGetLastError();
+                return fail(MPB_E_NOMEM, "cudaMalloc(2 x %zu) for the chain-carry segment arrays", bytes);
+            }
+            p->chunk_items = want;
+        }
+        if (!p->chain_log) {
+            long long ent = p->log_entries_req > 0 ? p->log_entries_req : std::max(4LL << 20, 64LL * p->sublen);
+            ent = (ent + mpb::LOG_SHARDS - 1) / mpb::LOG_SHARDS;
+            if (ent > 0x7fffffffLL) ent = 0x7fffffffLL;
+            const size_t bytes = sizeof(mpb::ChainLogEntry) * (size_t)ent * mpb::LOG_SHARDS;
+            if (cudaMalloc((void **)&p->chain_log, bytes) != cudaSuccess) { cudaGetLastError(); return fail(MPB_E_NOMEM, "cudaMalloc(%zu) for the chain-carry candidate log", bytes); }
+            p->log_shard_cap = (unsigned)ent;
+        }
+        const int blocks = (p->sublen + seg - 1) / seg;
+        if (blocks > p->inv_blocks) {
+            if (p->inv_blockmax) cudaFree(p->inv_blockmax);
+            p->inv_blockmax = nullptr; p->inv_blocks = 0;
+            if (cudaMalloc((void **)&p->inv_blockmax, sizeof(double) * (size_t)blocks) != cudaSuccess) { cudaGetLastError(); return fail(MPB_E_NOMEM, "cudaMalloc for the inverse-norm block maxima"); }
+            p->inv_blocks = blocks;
+        }
+    }
     return MPB_OK;
 }
 
@@ -386,7 +455,7 @@ int mpb_plan_precompute(mpb_plan *p) {
     int rc = plan_build_table(p);
     if (rc != MPB_OK) return rc;
     CU(cudaEventRecord(p->ev[2], s));
-    if (p->flags & MPB_FLAG_SEQ_MEAN) CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, s));
+    if (p->seq_mean) CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, s));
     else CU(mpb::launch_mu_window(p->T, p->n, p->m, p->mu, s));
     if (p->dtype == MPB_F64) CU(mpb::launch_stats_f64(p->T, p->mu, p->n, p->m, (double *)p->df_dg, (double *)p->inv, (double *)p->qt0, s));
     else CU(mpb::launch_stats_f32(p->T, p->mu, p->n, p->m, (float *)p->df_dg, (float *)p->inv, (float *)p->qt0, s));
@@ -394,9 +463,17 @@ int mpb_plan_precompute(mpb_plan *p) {
     else CU(mpb::launch_norm_f32((const float *)p->inv, p->sublen, p->np, (float *)p->nm, (float *)p->mnc, s));
     CU(mpb::launch_profile_init(p->prof, p->np, s));
     p->tm.launches = 4;
+    if (p->chain_fix) {
+        CU(mpb::launch_profile_init(p->fin, p->np, s));
+        CU(cudaMemsetAsync(p->chain_stats, 0, 4 * sizeof(unsigned long long), s));
+        CU(mpb::launch_inv_block_max((const double *)p->inv, p->sublen, p->seg_rows_eff, p->inv_blockmax, s));
+        p->tm.launches += 2;
+    }
     if (!(p->flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_SEED))) {
-        if (p->dtype == MPB_F64) CU(mpb::launch_seed_profile_f64(p->T, p->mu, (const double *)p->inv, p->n, p->m, p->excl, p->prof, s));
-        else CU(mpb::launch_seed_profile_f32(p->T, p->mu, (const float *)p->inv, p->n, p->m, p->excl, p->prof, s));
+        // chain-carry mode: the seed is a borrowed lower bound (4 margins below the cell, index -1), never a result
+        const double borrow = p->chain_fix ? std::ldexp(1.0, -p->margin_log2) : 0.0;
+        if (p->dtype == MPB_F64) CU(mpb::launch_seed_profile_f64(p->T, p->mu, (const double *)p->inv, p->n, p->m, p->excl, p->prof, borrow, s));
+        else CU(mpb::launch_seed_profile_f32(p->T, p->mu, (const float *)p->inv, p->n, p->m, p->excl, p->prof, 0.0, s));
         p->tm.launches += 1;
     }
     CU(cudaEventRecord(p->ev[3], s));
@@ -455,19 +532,65 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
             p->tm.launches += sl.items > 0 ? 2 : 0;
         }
     }
-    if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->mnc, (const double *)p->qt0, p->prof, tl, s));
-    else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->mnc, (const float *)p->qt0, p->prof, tl, s));
+    if (p->chain_fix && tl.items > 0) {
+        // chain-carry mode: launch chunks of whole bands that fit the S_k / E_k arrays; each chunk = tile kernel (candidates into
+        // the log) + carry scan + resolve into the result profile
+        int lb = lb_begin;
+        while (lb < lb_end) {
+            int hi = lb + 1;
+            while (hi < lb_end && (long long)p->table_host[hi + 1] - p->table_host[lb] <= p->chunk_items) ++hi;
+            mpb::TileLaunch cl = tl;
+            cl.item_begin = p->table_host[lb];
+            cl.items = (long long)p->table_host[hi] - cl.item_begin;
+            cl.chain.seg_seed = p->seg_seed; cl.chain.seg_end = p->seg_end; cl.chain.log = p->chain_log; cl.chain.log_count = p->log_count;
+            cl.chain.shard_cap = p->log_shard_cap; cl.chain.item_base = cl.item_begin;
+            const double margin = std::ldexp(1.0, -p->margin_log2);
+            cl.chain.margin = margin;
+            cl.chain.key_margin = (1 << std::max(0, 21 - p->margin_log2)) + 1;
+            CU(cudaMemsetAsync(p->log_count, 0, sizeof(unsigned long long) * 16 * mpb::LOG_SHARDS, s));
+            CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->mnc, (const double *)p->qt0, p->prof, cl, s));
+            CU(mpb::launch_chain_resolve(cl, lb, hi, (const double *)p->inv, p->inv_blockmax, p->prof, p->fin, p->chain_stats, s));
+            p->tm.launches += cl.items > 0 ? 3 : 0;
+            lb = hi;
+        }
+    } else {
+        if (p->dtype == MPB_F64) CU(mpb::launch_tiles_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->mnc, (const double *)p->qt0, p->prof, tl, s));
+        else CU(mpb::launch_tiles_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->mnc, (const float *)p->qt0, p->prof, tl, s));
+        p->tm.launches += tl.items > 0 ? 1 : 0;
+    }
     CU(cudaEventRecord(p->ev[5], s));
-    p->tm.launches += tl.items > 0 ? 1 : 0;
     return MPB_OK;
 }
 
 int mpb_plan_compute(mpb_plan *p) { return mpb_plan_compute_bands(p, 0, -1); }
 
+// which profile export / mask_index / import / merge_peers address in the chain-carry mode
+static mpb::ProfileEntry *merge_profile(mpb_plan *p) { return p->chain_fix && !p->merge_thresholds ? p->fin : p->prof; }
+
+int mpb_plan_merge_select(mpb_plan *p, int thresholds) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    p->merge_thresholds = thresholds != 0;
+    return MPB_OK;
+}
+
+int mpb_plan_set_chain_margin(mpb_plan *p, int log2_inverse) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    if (log2_inverse < 8 || log2_inverse > 21) return fail(MPB_E_INVALID, "the chain-carry margin is 2^-k with 8 <= k <= 21 (got %d)", log2_inverse);
+    p->margin_log2 = log2_inverse;
+    return MPB_OK;
+}
+
+int mpb_plan_set_log_entries(mpb_plan *p, int64_t entries) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    if (p->chain_log) { CU(cudaSetDevice(p->ctx->device)); CU(cudaStreamSynchronize(p->ctx->stream)); cudaFree(p->chain_log); p->chain_log = nullptr; }
+    p->log_entries_req = entries > 0 ? entries : -1; p->table_dirty = true;
+    return MPB_OK;
+}
+
 int mpb_plan_export(mpb_plan *p, void *corr_out, void *index_out) {
     if (!p || !corr_out || !index_out) return fail(MPB_E_INVALID, "null argument");
     CU(cudaSetDevice(p->ctx->device));
-    CU(mpb::launch_export(p->prof, p->sublen, (double *)corr_out, (int32_t *)index_out, p->ctx->stream));
+    CU(mpb::launch_export(merge_profile(p), p->sublen, (double *)corr_out, (int32_t *)index_out, p->ctx->stream));
     p->tm.launches += 1;
     return MPB_OK;
 }
@@ -475,7 +598,7 @@ int mpb_plan_export(mpb_plan *p, void *corr_out, void *index_out) {
 int mpb_plan_mask_index(mpb_plan *p, const void *corr_max, void *index) {
     if (!p || !corr_max || !index) return fail(MPB_E_INVALID, "null argument");
     CU(cudaSetDevice(p->ctx->device));
-    CU(mpb::launch_mask_index(p->prof, p->sublen, (const double *)corr_max, (int32_t *)index, p->ctx->stream));
+    CU(mpb::launch_mask_index(merge_profile(p), p->sublen, (const double *)corr_max, (int32_t *)index, p->ctx->stream));
     p->tm.launches += 1;
     return MPB_OK;
 }
@@ -483,7 +606,7 @@ int mpb_plan_mask_index(mpb_plan *p, const void *corr_max, void *index) {
 int mpb_plan_import(mpb_plan *p, const void *corr, const void *index) {
     if (!p || !corr || !index) return fail(MPB_E_INVALID, "null argument");
     CU(cudaSetDevice(p->ctx->device));
-    CU(mpb::launch_import(p->prof, p->sublen, (const double *)corr, (const int32_t *)index, p->ctx->stream));
+    CU(mpb::launch_import(merge_profile(p), p->sublen, (const double *)corr, (const int32_t *)index, p->ctx->stream));
     p->tm.launches += 1;
     return MPB_OK;
 }
@@ -507,7 +630,8 @@ int mpb_plan_merge_peers(mpb_plan *p, mpb_plan *const *others, int count) {
         CU(cudaEventRecord(o->ev[7], o->ctx->stream));
         CU(cudaSetDevice(p->ctx->device));
         CU(cudaStreamWaitEvent(p->ctx->stream, o->ev[7], 0));
-        CU(mpb::launch_merge_peer(p->prof, o->prof, p->sublen, p->ctx->stream));
+        if (p->chain_fix != o->chain_fix) return fail(MPB_E_INVALID, "peer plan %d runs in a different mode", k);
+        CU(mpb::launch_merge_peer(merge_profile(p), merge_profile(o), p->sublen, p->ctx->stream));
         p->tm.launches += 1;
     }
     return MPB_OK;
@@ -516,9 +640,23 @@ int mpb_plan_merge_peers(mpb_plan *p, mpb_plan *const *others, int count) {
 int mpb_plan_finalize(mpb_plan *p) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     CU(cudaSetDevice(p->ctx->device));
-    CU(mpb::launch_finalize(p->prof, p->sublen, p->m, p->MP, p->MPI, p->corr, p->ctx->stream));
+    CU(mpb::launch_finalize(p->chain_fix ? p->fin : p->prof, p->sublen, p->m, p->MP, p->MPI, p->corr, p->ctx->stream));
     CU(cudaEventRecord(p->ev[6], p->ctx->stream));
     p->tm.launches += 1;
+    return MPB_OK;
+}
+
+// chain-carry mode: a candidate log that overflowed dropped candidates -- the result may miss a maximum, so that is an error
+static int chain_check(mpb_plan *p) {
+    if (!p->chain_fix) return MPB_OK;
+    unsigned long long st[4] = {0, 0, 0, 0};
+    CU(cudaMemcpy(st, p->chain_stats, sizeof st, cudaMemcpyDeviceToHost));
+    if (st[2]) return fail(MPB_E_NOMEM, "the chain-carry near-tie log overflowed (%u entries per sub-log): raise it with mpb_plan_set_log_entries", p->log_shard_cap);
+    double bound; memcpy(&bound, &st[3], sizeof bound);
+    const double margin = std::ldexp(1.0, -p->margin_log2);
+    if (2.0 * bound > margin * MPB_CHAIN_FLOOR)      // two candidates further apart than the margin could have changed order
+        return fail(MPB_E_INVALID, "chain-carry corrections are bounded by %.3g, too large for the near-tie margin 2^-%d (needs 2 * bound <= margin / 64): "
+                                   "raise it with mpb_plan_set_chain_margin, or use MPB_FLAG_NO_RESEED", bound, p->margin_log2);
     return MPB_OK;
 }
 
@@ -531,7 +669,7 @@ int mpb_plan_download(mpb_plan *p, double *MP_host, int32_t *MPI_host, double *c
     if (corr_host) CU(cudaMemcpyAsync(corr_host, p->corr, sizeof(double) * (size_t)p->sublen, cudaMemcpyDeviceToHost, s));
     CU(cudaEventRecord(p->ev[7], s));
     CU(cudaStreamSynchronize(s));
-    return MPB_OK;
+    return chain_check(p);
 }
 
 void *mpb_plan_mp_device_ptr(mpb_plan *p) { return p ? p->MP : nullptr; }
@@ -575,6 +713,15 @@ int mpb_plan_timings(mpb_plan *p, mpb_timings *out) {
     t.filter_hits = (int64_t)cnt[0];
     t.slow_updates = (int64_t)cnt[1];
     t.replays = (int64_t)cnt[2];
+    t.chain_candidates = 0; t.chain_max_correction = 0.0; t.chain_bound = 0.0; t.chain_margin = 0.0;
+    if (p->chain_fix) {
+        unsigned long long st[4] = {0, 0, 0, 0};
+        CU(cudaMemcpy(st, p->chain_stats, sizeof st, cudaMemcpyDeviceToHost));
+        memcpy(&t.chain_max_correction, &st[0], sizeof(double));
+        memcpy(&t.chain_bound, &st[3], sizeof(double));
+        t.chain_candidates = (int64_t)st[1];
+        t.chain_margin = std::ldexp(1.0, -p->margin_log2);
+    }
     *out = t;
     return MPB_OK;
 }

@@ -63,15 +63,15 @@ constexpr int ROW_BLOCKS = ROWS_STAGED / RB;
 constexpr int COL_SLOTS = DPT * COL_STRIDE;
 constexpr unsigned FULL = 0xffffffffu;
 
-struct __align__(16) Winner { double v; int slot; int idx; };
+// A cell that improved (or, in the chain-carry mode, came within the margin of) the warp's view of a slot:
+// code = index of the cell in the hit buffer (hit * DPT + j) | role << 16 (0: the cell's column slot, 1: its row slot).
+struct __align__(16) Winner { double v; int code; int pad; };
+struct __align__(16) WarpLog { ChainLogEntry *log; unsigned long long *count; unsigned cap; int km; double mu; };   // chain-carry mode: this warp's sub-log, the near-tie margin, and the margin in high-word ulps (lower_key)
 #ifndef MPB_WCAP
 #define MPB_WCAP 96
 #endif
 #ifndef MPB_STAGE_BATCH
 #define MPB_STAGE_BATCH 1
-#endif
-#ifndef MPB_PARK_EXACT
-#define MPB_PARK_EXACT 0                        // 1: exact P test before a thread-row is parked (v4..v7)
 #endif
 // Blocks of the hot loop per loop iteration.  With 2 the checkpoint / QT register sets alternate and ptxas drops ~27 of
 // the ~38 loop-carried register copies per block; the fp64 loop is issue-bound (a DFMA costs two issue slots, every
@@ -84,7 +84,7 @@ struct __align__(16) Winner { double v; int slot; int idx; };
 #define MPB_HOT_UNROLL_F32 1
 #endif
 template <typename T> __host__ __device__ constexpr int hot_unroll() { return sizeof(T) == 8 ? MPB_HOT_UNROLL_F64 : MPB_HOT_UNROLL_F32; }
-constexpr int WCAP = MPB_WCAP;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners)
+constexpr int WCAP = MPB_WCAP;                  // winner list capacity (a drain pass adds up to 32 column + 4 row winners; 32 + 32 in the chain-carry mode)
 
 template <typename T>
 struct WarpSmem {
@@ -92,7 +92,7 @@ struct WarpSmem {
     static constexpr int NK = (COL_STRIDE + 3) / 4 * 4;
     static constexpr int HITS_BYTES = HCAP * DPT * (int)sizeof(T) + HCAP * 8;
     static constexpr int BYTES = ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * (int)sizeof(T) + COL_SLOTS * 8 +
-                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16 + WCAP * 16;
+                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16 + WCAP * 16 + (int)sizeof(WarpLog);
     T2 *rowA;         // [i] = {df_r, dg_r}
     double2 *rowC;    // [i] = {best correlation of the row as this warp knows it, inv_r}
     T2 *colA;         // [slot(x)] = {df_c, dg_c}
@@ -106,6 +106,7 @@ struct WarpSmem {
     T *wK;            // [q] = min of best_c * norm_c over the same columns (key precision)
     unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] blocks replayed
     Winner *wlist;    // cells that improved the warp's view of a slot, waiting for the profile update
+    WarpLog *wlog;    // chain-carry mode: where this warp appends its candidates
     __device__ __forceinline__ explicit WarpSmem(unsigned char *base) {
         rowA = reinterpret_cast<T2 *>(base);
         rowC = reinterpret_cast<double2 *>(rowA + ROWS_STAGED);
@@ -120,6 +121,7 @@ struct WarpSmem {
         wK = mncK + NK;
         stat = reinterpret_cast<unsigned *>(wK + NK);
         wlist = reinterpret_cast<Winner *>(stat + 4);
+        wlog = reinterpret_cast<WarpLog *>(wlist + WCAP);
     }
 };
 static_assert(WarpSmem<double>::BYTES % 16 == 0 && WarpSmem<float>::BYTES % 16 == 0, "warp slices stay 16-byte aligned");
@@ -164,6 +166,16 @@ __device__ __forceinline__ float corr_of(float qt, float ir, float ic) { return 
 __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 
+// Chain-carry mode: a threshold lowered by (at least) the near-tie margin, on the ALU pipe.  hw = high word of a
+// non-negative double; km = margin in high-word ulps (one ulp is 2^-21 .. 2^-20 of the value): the result is >= km ulps
+// lower for values above CHAIN_FLOOR = 2^-6 (exponent field 1017) and a constant km * 2^-26 lower below it (the shift
+// grows by one per binade), which is chain_lower()'s rule rounded towards "lower".
+__device__ __forceinline__ int lower_key(int hw, int km) {
+    const int sh = min(max(1017 - (hw >> 20), 0), 10);
+    return max(hw - (km << sh), 0);
+}
+__device__ __forceinline__ double lower_thr(double v, int km) { return __hiloint2double(lower_key(__double2hiint(v), km), __double2loint(v)); }
+
 extern __shared__ __align__(16) unsigned char smem_raw[];
 
 // 64-bit max on a shared-memory double that is known to be >= +0.0 (positive IEEE patterns order like integers)
@@ -179,17 +191,62 @@ __device__ __forceinline__ double smem_max_pos(double *addr, double v) {
 // thread-row -- of the row's best.  Only cells that improve that view touch the profile in HBM/L2, with a 128-bit
 // compare-and-swap (mp_common.cuh: larger corr wins, equal corr -> smaller index).  Warp-collective.
 // ---------------------------------------------------------------------------------------------
-// applies the winner list to the profile: one entry per lane, so the memory round trips of a whole batch overlap
-template <typename T>
-__device__ __forceinline__ unsigned apply_winners(WarpSmem<T> &S, int cnt, ProfileEntry *prof, int lane) {
+// Chain-carry mode: (corr, index) max into a threshold slot with the three-way rule of mp_common.cuh.  A candidate
+// more than the margin above the slot's best replaces it, one more than the margin below is dropped, and within the
+// margin the loser of the comparison -- the candidate, or the entry it replaces -- goes to the near-tie log.  Entries
+// with index -1 (borrowed lower bounds) are thresholds, not cells: they are never logged.
+__device__ __forceinline__ void log_near_tie(const WarpLog *wl, double corr, int slot, int idx) {
+    const unsigned long long pos = atomicAdd(wl->count, 1ull);
+    if (pos < wl->cap) { ChainLogEntry le; le.corr = corr; le.slot = slot; le.index = idx; wl->log[pos] = le; }
+}
+__device__ __forceinline__ double profile_update_log(ProfileEntry *prof, int slot_id, double v, int idx, const WarpLog *wl) {
+    ProfileEntry *slot = prof + slot_id;
+    const double mu = wl->mu;
+    unsigned long long clo, chi, olo, ohi;
+    asm volatile("ld.global.relaxed.gpu.v2.u64 {%0,%1}, [%2];" : "=l"(clo), "=l"(chi) : "l"(slot) : "memory");
+    const unsigned long long nlo = (unsigned long long)__double_as_longlong(v);
+    const unsigned long long nhi = (unsigned long long)(unsigned)idx;
+    while (true) {
+        const double cv = __longlong_as_double((long long)clo);
+        const unsigned ci = (unsigned)chi;
+        const bool near = v >= chain_lower(cv, mu) && cv >= chain_lower(v, mu);
+        if (!(v > cv || (v == cv && (unsigned)idx < ci))) {
+            if (near && !(v == cv && (unsigned)idx == ci)) log_near_tie(wl, v, slot_id, idx);
+            break;
+        }
+        asm volatile(
+            "{\n .reg .b128 c, d, o;\n mov.b128 c, {%2, %3};\n mov.b128 d, {%4, %5};\n"
+            " atom.global.relaxed.gpu.cas.b128 o, [%6], c, d;\n mov.b128 {%0, %1}, o;\n}"
+            : "=l"(olo), "=l"(ohi) : "l"(clo), "l"(chi), "l"(nlo), "l"(nhi), "l"(slot) : "memory");
+        if (olo == clo && ohi == chi) {
+            if (near && ci != 0xffffffffu) log_near_tie(wl, cv, slot_id, (int)ci);
+            clo = nlo;
+            break;
+        }
+        clo = olo; chi = ohi;
+    }
+    return __longlong_as_double((long long)clo);
+}
+
+// applies the winner list to the profile: one entry per lane, so the memory round trips of a whole batch overlap.
+template <typename T, bool LOG>
+__device__ __forceinline__ unsigned apply_winners(WarpSmem<T> &S, int cnt, int r0, int c0, ProfileEntry *prof, int lane) {
     unsigned wins = 0;
     __syncwarp();
-    for (int e = lane; e < cnt; e += 32) { const Winner w = S.wlist[e]; wins += profile_update(prof + w.slot, w.v, w.idx) == w.v; }
+    for (int e = lane; e < cnt; e += 32) {
+        const Winner w = S.wlist[e];
+        const int cell = w.code & 0xffff, h = cell / DPT, j = cell % DPT;
+        const int2 mt = S.hitM[h];
+        const int row = r0 + mt.x, col = c0 + mt.y + j;
+        const int slot = (w.code >> 16) ? row : col, idx = (w.code >> 16) ? col : row;
+        if (LOG) wins += profile_update_log(prof, slot, w.v, idx, S.wlog) == w.v;
+        else wins += profile_update(prof + slot, w.v, idx) == w.v;
+    }
     __syncwarp();
     return wins;
 }
 
-template <typename T>
+template <typename T, bool LOG>
 __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry *prof) {
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
@@ -209,8 +266,11 @@ __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry 
         const double2 rc = S.rowC[i];
         double pv = (double)corr_of(S.hitQ[h * DPT + j], (T)rc.y, S.colInv[p]);
         if (!act || !(pv > 0.0)) pv = -1.0;                  // P <= 0 and NaN never enter the profile (it starts at +0.0)
+        // chain-carry mode: the warp's views hold the bests LOWERED by the near-tie margin (lower_thr is monotone, so the
+        // max commutes with it): near misses are candidates too, and the replay's key tests need no extra work
+        const double pl = LOG ? lower_thr(fmax(pv, 0.0), S.wlog->km) : pv;
         bool cwin = pv > 0.0 && pv >= S.colBest[p];
-        if (cwin) cwin = pv >= smem_max_pos(&S.colBest[p], pv);
+        if (cwin) cwin = pv >= smem_max_pos(&S.colBest[p], pl);
         double bv = pv;                                      // best of the thread-row; ties keep the smaller column
         int bx = x;
 #pragma unroll
@@ -219,18 +279,31 @@ __device__ __noinline__ void drain_hits(int nhits, int r0, int c0, ProfileEntry 
             const int ox = __shfl_xor_sync(FULL, bx, sft);
             if (ov > bv || (ov == bv && ox < bx)) { bv = ov; bx = ox; }
         }
-        bool rwin = j == 0 && bv > 0.0 && bv >= rc.x;
-        if (rwin) rwin = bv >= smem_max_pos(&S.rowC[i].x, bv);
+        bool rwin;
+        int rcode = (h * DPT + (bx - mt.y)) | 0x10000;
+        if (!LOG) {
+            rwin = j == 0 && bv > 0.0 && bv >= rc.x;
+            if (rwin) rwin = bv >= smem_max_pos(&S.rowC[i].x, bv);
+        } else {
+            // the thread-row's best goes into the warp's view of the row; every cell of the thread-row within the
+            // margin of both that best and the row's previous best is a candidate
+            double old = rc.x;
+            const double bl = lower_thr(fmax(bv, 0.0), S.wlog->km);
+            if (j == 0 && bv > 0.0 && bv >= rc.x) old = smem_max_pos(&S.rowC[i].x, bl);
+            old = __shfl_sync(FULL, old, lane & ~(DPT - 1));
+            rwin = pv > 0.0 && pv >= fmax(old, bl);
+            rcode = e | 0x10000;
+        }
         const unsigned cm = __ballot_sync(FULL, cwin), rm = __ballot_sync(FULL, rwin);
         if (cm | rm) {
-            if (wcnt + __popc(cm) + __popc(rm) > WCAP) { wins += apply_winners<T>(S, wcnt, prof, lane); wcnt = 0; }
-            if (cwin) { Winner w; w.v = pv; w.slot = c0 + x; w.idx = r0 + i; S.wlist[wcnt + __popc(cm & lt)] = w; }
+            if (wcnt + __popc(cm) + __popc(rm) > WCAP) { wins += apply_winners<T, LOG>(S, wcnt, r0, c0, prof, lane); wcnt = 0; }
+            if (cwin) { Winner w; w.v = pv; w.code = e; w.pad = 0; S.wlist[wcnt + __popc(cm & lt)] = w; }
             wcnt += __popc(cm);
-            if (rwin) { Winner w; w.v = bv; w.slot = r0 + i; w.idx = c0 + bx; S.wlist[wcnt + __popc(rm & lt)] = w; }
+            if (rwin) { Winner w; w.v = LOG ? pv : bv; w.code = rcode; w.pad = 0; S.wlist[wcnt + __popc(rm & lt)] = w; }
             wcnt += __popc(rm);
         }
     }
-    if (wcnt) wins += apply_winners<T>(S, wcnt, prof, lane);
+    if (wcnt) wins += apply_winners<T, LOG>(S, wcnt, r0, c0, prof, lane);
     wins = __reduce_add_sync(FULL, wins);
     if (lane == 0) { S.stat[0] += nhits; S.stat[1] += wins; }
     __syncwarp();
@@ -255,40 +328,6 @@ __device__ __forceinline__ int max_key8(const T *q, int run) {
 
 template <typename T> struct QVec { T v[DPT]; };
 
-// Row t of a replayed block: lanes whose thread-row passed the snapshot test (`cand`) compute the exact
-// P = (QT * inv_r) * inv_c of their 8 cells and compare it with the warp's live view of the column / row bests;
-// thread-rows with a real improvement park their QT values.  One shared copy of this code serves all 8 rows of
-// the unrolled replay (instruction-cache footprint).  Warp-collective; returns the new hit count.
-template <typename T>
-__device__ __noinline__ int park_row(QVec<T> q, bool cand, int t, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
-    const int lane = threadIdx.x & 31;
-    WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
-    const int i = i0 + t, e0 = i0 / DPT + lane;
-    bool flagged = false;
-    if (cand) {
-        const double2 rc = S.rowC[i];
-        const T ir = (T)rc.y;
-#pragma unroll
-        for (int j = 0; j < DPT; ++j) {                      // column i + DPT*lane + j
-            const int p = ((t + j) % DPT) * COL_STRIDE + e0 + (t + j) / DPT;
-            const double pv = (double)corr_of(q.v[j], ir, S.colInv[p]);
-            flagged |= pv > 0.0 && (pv >= S.colBest[p] || pv >= rc.x);
-        }
-    }
-    const unsigned mk = __ballot_sync(FULL, flagged);
-    if (mk) {
-        if (flagged) {
-            const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
-#pragma unroll
-            for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = q.v[j];
-            S.hitM[pos] = make_int2(i, i + DPT * lane);
-        }
-        hitcnt += __popc(mk);
-        if (hitcnt > HDRAIN) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }
-    }
-    return hitcnt;
-}
-
 // ---------------------------------------------------------------------------------------------
 // Replay of one block.  The hot loop only knows that SOME cell of SOME lane's block passed the block-wide test.
 // The block is walked again from the QT values it started with -- same operands, same order, bit-identical QT --
@@ -296,12 +335,12 @@ __device__ __noinline__ int park_row(QVec<T> q, bool cand, int t, int i0, int r0
 // compared, as an integer, with the high word of the warp's view of the column's best and of the row's best.
 // On smooth series (random walks) the QT-domain window tests are too loose to be worth an intermediate step:
 // P lives within a percent of the best for whole neighbourhoods, and only a per-cell test in the P domain tells
-// improvements from near misses.  Rows in which a lane passes go through park_row (exact compare + park).
+// improvements from near misses.  Thread-rows in which a lane passes are parked for the drain.
 // Column operands slide through registers exactly as in the hot loop.  Warp-collective; returns the new hit count.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ int hi_word(const double *p) { return reinterpret_cast<const int *>(p)[1]; }
 
-template <typename T, bool STRICT>
+template <typename T, bool STRICT, bool LOG>
 __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31;
@@ -331,12 +370,8 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
         }
         const int a = __vimax3_s32(kp[0], kp[1], kp[2]), b = __vimax3_s32(kp[3], kp[4], kp[5]);
         cand |= __vimax3_s32(kp[6], kp[7], max(a, b)) >= max(__double2hiint(rc.x), 1);
-#if MPB_PARK_EXACT
-        if (__any_sync(FULL, cand)) hitcnt = park_row<T>(qc, cand, t, i0, r0, c0, hitcnt, prof);
-#else
         // Thread-rows that pass the high-word test are parked as they are: the drain repeats the comparison exactly, cell
-        // by cell, and a false candidate needs a P within 2^-20 of the current best (rare), so an exact test here
-        // (park_row: 16 DMUL + 24 DSETP per candidate lane behind a call) only duplicated the drain's work.
+        // by cell, and a false candidate needs a P within 2^-20 of the current best (rare).
         const unsigned mk = __ballot_sync(FULL, cand);
         if (mk) {
             if (cand) {
@@ -346,9 +381,8 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
                 S.hitM[pos] = make_int2(i, i + DPT * lane);
             }
             hitcnt += __popc(mk);
-            if (hitcnt > HDRAIN) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }
+            if (hitcnt > HDRAIN) { drain_hits<T, LOG>(hitcnt, r0, c0, prof); hitcnt = 0; }
         }
-#endif
         if (t + 1 < RB) {
             const T2 ra = S.rowA[i + 1];
             const T2 nd = S.colA[t * COL_STRIDE + e0 + 1];   // column entering the window: i + DPT*lane + DPT
@@ -413,12 +447,14 @@ __device__ __forceinline__ void reseed(T (&qt)[DPT], WarpSmem<T> &S, const doubl
 
 // item_start[lb] = first work item of this rank's local band lb (nlb + 1 entries)
 // counters[0] += thread-rows parked for the exact test, counters[1] += profile slots improved, counters[2] += blocks replayed
-template <typename T, bool STRICT>
+// LOG = chain-carry mode (mp_common.cuh): the item stores the QT values it started from and ended with, and the drain
+// logs near-best candidates for the resolve kernel; the profile `prof` then only carries the filter thresholds.
+template <typename T, bool STRICT, bool LOG>
 __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ mnc,
             const T *__restrict__ qt0, const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
             const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
-            unsigned long long *counters) {
+            unsigned long long *counters, const ChainFix cf) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
@@ -445,12 +481,29 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 
     int hitcnt = 0;                 // warp-uniform: hits parked in the buffer
     if (lane < 4) S.stat[lane] = 0;
+    if (LOG && lane == 0) {
+        const unsigned shard = (blockIdx.x * BAND_WARPS + warp) % LOG_SHARDS;
+        WarpLog wl; wl.log = cf.log + (size_t)shard * cf.shard_cap; wl.count = cf.log_count + shard * 16; wl.cap = cf.shard_cap;
+        wl.km = cf.key_margin; wl.mu = cf.margin;
+        *S.wlog = wl;
+    }
     const T sl = slack(T(0));
+    const int km = LOG ? cf.key_margin : 0;               // chain-carry mode: every staged best is lowered by the near-tie margin
 
     // Software pipeline: on entry to row i the registers hold QT(row i) already; the loop body takes the filter
     // keys of QT(row i), then issues the QT step to row i+1 BEFORE branching on the test, so the max-tree /
     // compare / vote latency of one row hides behind the FMAs of the next.  Each tile stages TILE_H + 1 rows.
-    bool first_tile = true;
+    {   // pipeline prologue: QT(row rbeg), operands straight from HBM/L2 (once per item)
+        const T2 ra = df_dg[rbeg];
+        const T2 *cp = df_dg + rbeg + d0w + lane * DPT;
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) { const T2 c = cp[j]; qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, c.x, c.y); }
+        if (LOG && seg > 0) {                              // S_k: what this segment's chain holds at its first row
+            double2 *dst = reinterpret_cast<double2 *>(cf.seg_seed + ((size_t)(item - cf.item_base) * BAND_W + warp * WARP_DIAGS + lane * DPT));
+#pragma unroll
+            for (int j = 0; j < DPT; j += 2) dst[j / 2] = make_double2((double)qt[j], (double)qt[j + 1]);
+        }
+    }
     for (int r0 = rbeg; r0 < rend; r0 += TILE_H) {
         const int c0 = r0 + d0w;
         __syncwarp();   // previous tile fully consumed
@@ -462,7 +515,8 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             if (i < ROWS_STAGED) {
                 S.rowA[i] = df_dg[r0 + i];
                 const T2 nv = nm[r0 + i];                       // {norm, inv}; norm = +inf on the padding
-                const double rbest = __ldcg(&prof[r0 + i].corr);
+                double rbest = __ldcg(&prof[r0 + i].corr);
+                if (LOG) rbest = lower_thr(rbest, km);
                 S.rowC[i] = make_double2(rbest, (double)nv.y);
                 const T best = max((T)rbest, tiny_best(T(0)));  // never 0: 0 * inf would be a NaN
                 rb.y = mul_rn(nv.x, sl);
@@ -493,6 +547,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
                 ca[k] = df_dg[c0 + x];
                 nv[k] = nm[c0 + x];                         // {norm_c, inv_c}
                 cb[k] = __ldcg(&prof[c0 + x].corr);
+                if (LOG) cb[k] = lower_thr(cb[k], km);
             }
 #pragma unroll
             for (int k = 0; k < NQI; ++k) { const int q = lane + 32 * k; mq[k] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0)); }
@@ -516,7 +571,8 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             const int p = col_slot(x);
             S.colA[p] = df_dg[c0 + x];
             const T2 nv = nm[c0 + x];                       // {norm_c, inv_c}
-            const double cbest = __ldcg(&prof[c0 + x].corr);
+            double cbest = __ldcg(&prof[c0 + x].corr);
+            if (LOG) cbest = lower_thr(cbest, km);
             S.colBest[p] = cbest;
             S.colInv[p] = nv.y;
             S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn((T)cbest, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
@@ -544,12 +600,6 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         for (int k = 0; k < DPT; ++k) {
             const T2 a = S.colA[k * COL_STRIDE + lane];
             cdf[k] = a.x; cdg[k] = a.y;
-        }
-        if (first_tile) {                                  // pipeline prologue: QT(row rbeg)
-            const T2 ra = S.rowA[0];
-#pragma unroll
-            for (int j = 0; j < DPT; ++j) qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[j], cdg[j]);
-            first_tile = false;
         }
         const T2 *rowA = S.rowA + 2;                       // [ii] = {df, dg} of row i + 2 (consumed one sub-step later)
         const T2 *colA = S.colA + lane + 1;
@@ -583,10 +633,16 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             const int ka = key_of(mul_rn(rk.x, cwn));
             const int kb = key_of(mul_rn(rk.y, cww));
             if (__builtin_expect(__any_sync(FULL, run > __vimin_s32_relu(ka, kb)), 0))
-                hitcnt = replay_block<T, STRICT>(qc, I * DPT, r0, c0, hitcnt, prof);
+                hitcnt = replay_block<T, STRICT, LOG>(qc, I * DPT, r0, c0, hitcnt, prof);
             rowA += DPT; colA += 1;
         }
-        if (hitcnt > 0) { drain_hits<T>(hitcnt, r0, c0, prof); hitcnt = 0; }   // candidates never outlive their tile
+        if (hitcnt > 0) { drain_hits<T, LOG>(hitcnt, r0, c0, prof); hitcnt = 0; }   // candidates never outlive their tile
+    }
+    if (LOG) {                                             // E_k: the chain's value at the first row of the next segment
+        const int item_e = blockIdx.x + item_begin;
+        double2 *dst = reinterpret_cast<double2 *>(cf.seg_end + ((size_t)(item_e - cf.item_base) * BAND_W + (threadIdx.x >> 5) * WARP_DIAGS + (threadIdx.x & 31) * DPT));
+#pragma unroll
+        for (int j = 0; j < DPT; j += 2) dst[j / 2] = make_double2((double)qt[j], (double)qt[j + 1]);
     }
     __syncwarp();
     if (counters && lane == 0 && S.stat[2]) {
@@ -803,12 +859,143 @@ static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *mnc, con
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
     if (p.seg_rows % TILE_H != 0 || p.seg_rows < 0) return cudaErrorInvalidValue;
+    const bool carry = p.chain.log != nullptr;
+    if (carry && (sizeof(T) != 8 || p.strict || p.seg_rows == 0)) return cudaErrorInvalidValue;
     const size_t smem = (size_t)cta_smem_bytes<T>();
-    auto kern = p.strict ? tile_kernel<T, true> : tile_kernel<T, false>;
+    auto kern = p.strict ? tile_kernel<T, true, false> : tile_kernel<T, false, false>;
+    if (carry) kern = tile_kernel<T, false, sizeof(T) == 8>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), mnc, qt0, p.series, p.mu,
-                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters);
+                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters, p.chain);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Chain carry, step 2: D_k(d) for every (band, warp, diagonal) of the chunk, in place of S_k.
+//   D_0 = 0,  D_k = D_{k-1} + (E_{k-1} - S_k)          (E - S first: the two are equal to ~1e-9 relative, so the
+// difference is exact and the carry accumulates without losing what it is made of)
+// One thread per diagonal of the chunk's bands; consecutive threads read consecutive doubles.
+// stats[3] = max over (k, d) of |D_k(d)| * (largest inv among the rows of segment k) * (largest inv among the columns
+// those rows meet on diagonal d), as double bits: an upper bound of the correction any P of the chunk can receive
+// (imax[j] = largest inv over rows [j * seg_rows, (j + 1) * seg_rows), from inv_block_max_kernel).
+// ---------------------------------------------------------------------------------------------
+__global__ void inv_block_max_kernel(const double *__restrict__ inv, int sublen, int seg_rows, double *__restrict__ imax) {
+    const int j = blockIdx.x;
+    double v = 0.0;
+    for (int i = j * seg_rows + threadIdx.x; i < min((j + 1) * seg_rows, sublen); i += blockDim.x) v = fmax(v, inv[i]);
+    __shared__ double red[32];
+    for (int sft = 16; sft; sft >>= 1) v = fmax(v, __shfl_xor_sync(FULL, v, sft));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) { for (int w = 1; w < (int)blockDim.x / 32; ++w) v = fmax(v, red[w]); imax[j] = v; }
+}
+
+__global__ void chain_scan_kernel(ChainFix cf, const int *__restrict__ item_start, int lb_begin, int lb_end, int nlb, int sublen, int excl, int seg_rows,
+                                  const double *__restrict__ imax, unsigned long long *stats) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lb = lb_begin + (int)(t / BAND_W), off = (int)(t % BAND_W);
+    double bound = 0.0;
+    if (lb < lb_end) {
+        const int band = item_start[nlb + 1 + lb];
+        const int d0w = excl + band * BAND_W + (off / WARP_DIAGS) * WARP_DIAGS;
+        const int d = excl + band * BAND_W + off;
+        const int nrows = sublen - d0w;                          // rows of the warp's first diagonal: its segment count
+        const int nseg = nrows > 0 ? (nrows + seg_rows - 1) / seg_rows : 0;
+        const int nblk = (sublen + seg_rows - 1) / seg_rows;
+        const size_t base = (size_t)(item_start[lb] - cf.item_base) * BAND_W + off;
+        double carry = 0.0;
+        if (nseg > 0) cf.seg_seed[base] = 0.0;
+        for (int k = 1; k < nseg; ++k) {
+            const double ek = cf.seg_end[base + (size_t)(k - 1) * BAND_W];
+            const double sk = cf.seg_seed[base + (size_t)k * BAND_W];
+            carry = __dadd_rn(carry, __dsub_rn(ek, sk));
+            cf.seg_seed[base + (size_t)k * BAND_W] = carry;
+            if ((long long)k * seg_rows + d < sublen) {          // the diagonal has cells in this segment
+                const int jc = (k * seg_rows + d) / seg_rows;
+                const double ic = fmax(imax[min(jc, nblk - 1)], imax[min(jc + 1, nblk - 1)]);
+                bound = fmax(bound, fabs(carry) * imax[k] * ic);
+            }
+        }
+    }
+    const unsigned hi = __reduce_max_sync(FULL, (unsigned)(__double_as_longlong(bound) >> 32) + (bound > 0.0 ? 1u : 0u));   // high word, rounded up
+    if ((threadIdx.x & 31) == 0 && hi) atomicMax(stats + 3, (unsigned long long)hi << 32);
+}
+
+// Chain carry, step 3: the carry of cell (r, c): P = P' + D_k(d) * inv_r * inv_c, the value the reference's unbroken chain
+// gives the cell (kernel/MatrixProfileKernelVanilla.cpp:81,84) to rounding.  Returns false when the cell's band is not one
+// of this launch chunk's (another rank's entry after a threshold merge, or an earlier chunk's: already resolved).
+struct ChainGeom { const int *item_start; int nlb, lb_begin, lb_end, excl, rank, world, seg_rows; };
+__device__ __forceinline__ bool chain_value(const ChainFix &cf, const ChainGeom &g, const double *__restrict__ inv, double corr, int slot, int index,
+                                            double *out, double *rel) {
+    if (index < 0) return false;
+    const int r = min(slot, index), c = max(slot, index);
+    const int gd = c - r - g.excl;
+    if (gd < 0) return false;
+    const int band = gd / BAND_W;
+    if (band % g.world != g.rank) return false;
+    const int lb = band / g.world;
+    if (lb < g.lb_begin || lb >= g.lb_end) return false;
+    const int k = r / g.seg_rows;
+    const double d = cf.seg_seed[(size_t)(g.item_start[lb] + k - cf.item_base) * BAND_W + gd % BAND_W];
+    const double corr_fix = d * inv[r] * inv[c];
+    *out = corr + corr_fix;
+    *rel = fabs(corr_fix) / corr;
+    return true;
+}
+
+// (a) every slot's surviving threshold entry, (b) every logged near tie -> the result profile, exact (corr, index) max.
+// stats[0] = largest relative correction applied (double bits), stats[1] += values resolved, stats[2] |= log overflow
+__global__ void chain_resolve_kernel(ChainFix cf, ChainGeom g, const double *__restrict__ inv, const ProfileEntry *__restrict__ prof, ProfileEntry *fin,
+                                     int sublen, unsigned long long *stats) {
+    double worst = 0.0;
+    unsigned mine = 0;
+    const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long i = t0; i < sublen; i += stride) {
+        const ProfileEntry e = prof[i];
+        double pv, rel;
+        if (e.corr > 0.0 && chain_value(cf, g, inv, e.corr, (int)i, e.index, &pv, &rel) && pv > 0.0) {
+            profile_update(fin + i, pv, e.index); worst = fmax(worst, rel); ++mine;
+        }
+    }
+    for (int shard = 0; shard < LOG_SHARDS; ++shard) {
+        unsigned long long cnt = cf.log_count[shard * 16];
+        if (cnt > cf.shard_cap) {                                // near ties were dropped: the host turns this into an error
+            if (t0 == 0) atomicOr(stats + 2, 1ull);
+            cnt = cf.shard_cap;
+        }
+        const ChainLogEntry *log = cf.log + (size_t)shard * cf.shard_cap;
+        for (long long e = t0; e < (long long)cnt; e += stride) {
+            const ChainLogEntry le = log[e];
+            double pv, rel;
+            if (chain_value(cf, g, inv, le.corr, le.slot, le.index, &pv, &rel) && pv > 0.0) {
+                profile_update(fin + le.slot, pv, le.index); worst = fmax(worst, rel); ++mine;
+            }
+        }
+    }
+    const unsigned hi = __reduce_max_sync(FULL, (unsigned)(__double_as_longlong(worst) >> 32));   // the high word is enough for a statistic
+    mine = __reduce_add_sync(FULL, mine);
+    if ((threadIdx.x & 31) == 0) {
+        if (hi) atomicMax(stats, (unsigned long long)hi << 32);
+        if (mine) atomicAdd(stats + 1, (unsigned long long)mine);
+    }
+}
+
+cudaError_t launch_inv_block_max(const double *inv, int sublen, int seg_rows, double *imax, cudaStream_t s) {
+    if (seg_rows <= 0) return cudaSuccess;
+    inv_block_max_kernel<<<(sublen + seg_rows - 1) / seg_rows, 256, 0, s>>>(inv, sublen, seg_rows, imax);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_chain_resolve(const TileLaunch &p, int lb_begin, int lb_end, const double *inv, const double *imax, const ProfileEntry *prof, ProfileEntry *fin,
+                                 unsigned long long *stats, cudaStream_t s) {
+    if (p.chain.log == nullptr || lb_end <= lb_begin) return cudaSuccess;
+    const long long threads = (long long)(lb_end - lb_begin) * BAND_W;
+    chain_scan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p.chain, p.item_start, lb_begin, lb_end, p.nlb, p.sublen, p.excl, p.seg_rows, imax, stats);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    ChainGeom g; g.item_start = p.item_start; g.nlb = p.nlb; g.lb_begin = lb_begin; g.lb_end = lb_end; g.excl = p.excl; g.rank = p.rank; g.world = p.world; g.seg_rows = p.seg_rows;
+    chain_resolve_kernel<<<1184, 256, 0, s>>>(p.chain, g, inv, prof, fin, p.sublen, stats);
     return cudaGetLastError();
 }
 

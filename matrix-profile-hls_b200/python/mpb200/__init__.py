@@ -20,7 +20,7 @@ import weakref
 import numpy as np
 
 F64, F32 = 0, 1
-FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED, FLAG_NO_SEED = 1, 2, 4, 8
+FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED, FLAG_NO_SEED, FLAG_NO_CHAIN_CARRY, FLAG_WINDOW_MEAN = 1, 2, 4, 8, 16, 32
 _LIB = None
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # matrix-profile-hls_b200/
 LIB_PATH = os.environ.get("MPB200_LIB") or os.path.join(_PKG_ROOT, "libmpb200.so")   # MPB200_LIB: tuning builds (csrc/Makefile VARIANT=)
@@ -45,7 +45,8 @@ class MpbError(RuntimeError):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("precompute_ms", C.c_double), ("compute_ms", C.c_double), ("finalize_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("cells", C.c_int64), ("slow_updates", C.c_int64),
-                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64), ("replays", C.c_int64)]
+                ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64), ("replays", C.c_int64),
+                ("chain_candidates", C.c_int64), ("chain_max_correction", C.c_double), ("chain_bound", C.c_double), ("chain_margin", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -57,7 +58,7 @@ EXPORTS = [
     "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
-    "mpb_plan_import", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
+    "mpb_plan_import", "mpb_plan_merge_select", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
     "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_useful_cells", "mpb_measure_fma_peak",
 ]
 
@@ -276,6 +277,16 @@ class Plan:
 
     def import_(self, corr_ptr, index_ptr):
         _chk(lib().mpb_plan_import(self._h, C.c_void_p(corr_ptr), C.c_void_p(index_ptr)))
+
+    def merge_select(self, thresholds):
+        """Chain-carry mode: export / import / merge_peers address the filter thresholds (True) or the result (False)."""
+        _chk(lib().mpb_plan_merge_select(self._h, C.c_int(1 if thresholds else 0)))
+
+    def set_chain_margin(self, log2_inverse):
+        _chk(lib().mpb_plan_set_chain_margin(self._h, C.c_int(log2_inverse)))
+
+    def set_log_entries(self, entries):
+        _chk(lib().mpb_plan_set_log_entries(self._h, C.c_int64(entries)))
 
     def merge_peers(self, others):
         arr = (C.c_void_p * len(others))(*[o._h for o in others])
