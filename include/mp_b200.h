@@ -47,6 +47,8 @@ extern "C" {
 #define MPB_FLAG_NO_CHAIN_CARRY 16u /* fp64: keep the re-seeded segments' own values (round 1's fast mode: drifts from the
                                   reference by up to 6e-9 on a 2^20-sample random walk) */
 #define MPB_FLAG_WINDOW_MEAN 32u /* fp64: exact window means instead of the reference's running mean (no sequential scan) */
+#define MPB_FLAG_MU_WALK 64u   /* running mean by one thread walking the chain (measurement aid: the default evaluates the same
+                                  recurrence as a verified segmented scan, csrc/precompute.cu, and gives the same bits) */
 
 typedef struct mpb_context mpb_context; /* replaces OpenCL::Context   (OpenCL.hpp:73-107, 294-317) */
 typedef struct mpb_buffer mpb_buffer;   /* replaces OpenCL::Buffer<T> (OpenCL.hpp:109-211) */
@@ -172,6 +174,9 @@ void *mpb_plan_mpi_device_ptr(mpb_plan *plan);                      /* int32[n-m
 /* The precomputed InputDataPack[n-m+1] (reference layout), for parity checks of kernel (1). */
 int mpb_plan_download_input(mpb_plan *plan, void *input_host);
 int mpb_plan_timings(mpb_plan *plan, mpb_timings *out);
+/* After mpb_plan_precompute with the reference's running mean: *walked = 1 when the chain was walked element by element
+ * (MPB_FLAG_MU_WALK, or the verified segmented-scan formulation failed a check and fell back), 0 when the scan stood. */
+int mpb_plan_mu_walked(mpb_plan *plan, int *walked);
 int64_t mpb_useful_cells(int n, int m);
 
 /* ---- measurement support ---- */

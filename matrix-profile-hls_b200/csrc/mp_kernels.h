@@ -8,7 +8,11 @@
 namespace mpb {
 
 // kernel (1): precompute.cu
-cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, cudaStream_t s);      // the reference's sequential running mean
+// the reference's sequential running mean, bit for bit: mode 0 = one thread walks the chain; mode 1 = segmented-scan formulation with
+// every step verified (precompute.cu), the walk only as its fallback.  scratch: mu_scan_scratch_bytes(n, m) device bytes (mode 1)
+cudaError_t launch_mu_scan(const double *T, int n, int m, double *mu, void *scratch, int mode, cudaStream_t s);
+size_t mu_scan_scratch_bytes(int n, int m);
+size_t mu_scan_bad_offset(int n, int m);
 cudaError_t launch_mu_window(const double *T, int n, int m, double *mu, cudaStream_t s);    // exact window means (parallel)
 cudaError_t launch_stats_f64(const double *T, const double *mu, int n, int m, double *df_dg, double *inv, double *qt0, cudaStream_t s);
 cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, float *df_dg, float *inv, float *qt0, cudaStream_t s);

@@ -91,6 +91,7 @@ struct mpb_plan {
     double *MP = nullptr, *corr = nullptr;
     int32_t *MPI = nullptr;
     unsigned long long *slow_counter = nullptr;
+    void *mu_scratch = nullptr;           // work space of the parallel running-mean kernels (seq_mean only)
     int *hint = nullptr;                  // np high words: lower bounds of the slots' best correlation from the sketch pass
     int sketch_bands = -1;                // local bands the sketch pass covers (-1 = default, 0 = off)
     int seg_rows = -1;                    // requested (-1 = auto)
@@ -299,7 +300,7 @@ int mpb_plan_destroy(mpb_plan *p) {
     cudaSetDevice(p->ctx->device);
     cudaStreamSynchronize(p->ctx->stream);
     void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start, p->hint,
-                    p->fin, p->seg_seed, p->seg_end, p->chain_log, p->log_count, p->chain_stats, p->inv_blockmax};
+                    p->fin, p->seg_seed, p->seg_end, p->chain_log, p->log_count, p->chain_stats, p->inv_blockmax, p->mu_scratch};
     for (void *q : ptrs) if (q) cudaFree(q);
     for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
     delete p;
@@ -346,6 +347,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
     ALLOC(p->slow_counter, 4 * sizeof(unsigned long long));
     ALLOC(p->hint, sizeof(int) * np);
+    if (p->seq_mean && !(flags & MPB_FLAG_MU_WALK)) ALLOC(p->mu_scratch, mpb::mu_scan_scratch_bytes(n, m));
     if (p->chain_fix) {
         ALLOC(p->fin, sizeof(mpb::ProfileEntry) * np);
         ALLOC(p->log_count, sizeof(unsigned long long) * 16 * mpb::LOG_SHARDS);
@@ -455,7 +457,7 @@ int mpb_plan_precompute(mpb_plan *p) {
     int rc = plan_build_table(p);
     if (rc != MPB_OK) return rc;
     CU(cudaEventRecord(p->ev[2], s));
-    if (p->seq_mean) CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, s));
+    if (p->seq_mean) CU(mpb::launch_mu_scan(p->T, p->n, p->m, p->mu, p->mu_scratch, (p->flags & MPB_FLAG_MU_WALK) ? 0 : 1, s));
     else CU(mpb::launch_mu_window(p->T, p->n, p->m, p->mu, s));
     if (p->dtype == MPB_F64) CU(mpb::launch_stats_f64(p->T, p->mu, p->n, p->m, (double *)p->df_dg, (double *)p->inv, (double *)p->qt0, s));
     else CU(mpb::launch_stats_f32(p->T, p->mu, p->n, p->m, (float *)p->df_dg, (float *)p->inv, (float *)p->qt0, s));
@@ -689,6 +691,19 @@ int mpb_plan_download_input(mpb_plan *p, void *input_host) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     cudaFree(tmp);
     CU(e);
+    return MPB_OK;
+}
+
+int mpb_plan_mu_walked(mpb_plan *p, int *walked) {
+    if (!p || !walked) return fail(MPB_E_INVALID, "null argument");
+    *walked = 0;
+    if (!p->seq_mean) return MPB_OK;
+    if (!p->mu_scratch) { *walked = 1; return MPB_OK; }
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaStreamSynchronize(p->ctx->stream));
+    int bad = 0;
+    CU(cudaMemcpy(&bad, (const char *)p->mu_scratch + mpb::mu_scan_bad_offset(p->n, p->m), sizeof bad, cudaMemcpyDeviceToHost));
+    *walked = bad != 0;
     return MPB_OK;
 }
 

@@ -20,7 +20,7 @@ import weakref
 import numpy as np
 
 F64, F32 = 0, 1
-FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED, FLAG_NO_SEED, FLAG_NO_CHAIN_CARRY, FLAG_WINDOW_MEAN = 1, 2, 4, 8, 16, 32
+FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED, FLAG_NO_SEED, FLAG_NO_CHAIN_CARRY, FLAG_WINDOW_MEAN, FLAG_MU_WALK = 1, 2, 4, 8, 16, 32, 64
 _LIB = None
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # matrix-profile-hls_b200/
 LIB_PATH = os.environ.get("MPB200_LIB") or os.path.join(_PKG_ROOT, "libmpb200.so")   # MPB200_LIB: tuning builds (csrc/Makefile VARIANT=)
@@ -59,7 +59,7 @@ EXPORTS = [
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_merge_select", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
-    "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_useful_cells", "mpb_measure_fma_peak",
+    "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_plan_mu_walked", "mpb_useful_cells", "mpb_measure_fma_peak",
 ]
 
 
@@ -309,6 +309,11 @@ class Plan:
         out = np.empty(self.sublen, IN_F64 if self.dtype == F64 else IN_F32)
         _chk(lib().mpb_plan_download_input(self._h, _vp(out)))
         return out
+
+    def mu_walked(self):
+        w = C.c_int(0)
+        _chk(lib().mpb_plan_mu_walked(self._h, C.byref(w)))
+        return bool(w.value)
 
     def timings(self):
         t = Timings()

@@ -493,3 +493,35 @@ def test_fp32_at_2p20_against_the_double_chain(mp, ctx, oracle, strict_2p20, kin
     for i in bad:
         a, b = oracle.exact_corr(T, 256, i, MPI[i]), oracle.exact_corr(T, 256, i, MPI0[i])
         assert abs(a - b) <= 1e-4, (i, MPI[i], MPI0[i], a, b)
+
+
+def _mu_series(kind, n, rng):
+    if kind == "uniform": return rng.random(n)
+    if kind == "walk": return np.cumsum(rng.standard_normal(n))
+    if kind == "noise0": return rng.standard_normal(n)                       # mean hovers around zero: mostly hard steps
+    if kind == "near1": return np.cumsum(rng.standard_normal(n)) * 1e-3 + 1.0  # mean keeps crossing a binade boundary
+    if kind == "dyadic": return np.round(rng.random(n) * 8) / 8                # exact ties of d / ulp
+    if kind == "tiny": return (rng.random(n) - 0.5) * 1e-300
+    if kind == "const": return np.full(n, 0.3)
+    if kind == "big": return np.cumsum(rng.standard_normal(n)) * 1e6
+    raise KeyError(kind)
+
+
+@pytest.mark.parametrize("kind,n,m", [("uniform", 1 << 20, 256), ("walk", 1 << 20, 256), ("noise0", 1 << 18, 64), ("near1", 1 << 18, 128),
+                                      ("dyadic", 1 << 18, 32), ("tiny", 1 << 17, 32), ("const", 1 << 16, 32), ("big", 1 << 18, 1024),
+                                      ("walk", 70001, 4096), ("uniform", 5000, 9)])
+def test_running_mean_scan_equals_the_walk(mp, ctx, kind, n, m):
+    """The reference's running mean (HostSideComputation.hpp:23,29) as a verified segmented scan == the same recurrence
+    walked element by element (MPB_FLAG_MU_WALK, which the golden tests pin to the reference), byte for byte over the
+    whole InputDataPack array, and the scan must have passed its own verification (no fallback to the walk)."""
+    T = _mu_series(kind, n, np.random.default_rng(7))
+    packs = []
+    for flags in (mp.FLAG_SEQ_MEAN, mp.FLAG_SEQ_MEAN | mp.FLAG_MU_WALK):
+        plan = mp.Plan(ctx, n, m, mp.F64, flags)
+        plan.upload_series(T)
+        plan.precompute()
+        packs.append(plan.download_input())
+        walked = plan.mu_walked()
+        assert walked == bool(flags & mp.FLAG_MU_WALK)
+        plan.close()
+    assert packs[0].tobytes() == packs[1].tobytes()
