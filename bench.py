@@ -2,20 +2,23 @@
 """bench.py -- headline benchmark of the B200 matrix-profile engine (BASELINE.json metric).
 
 Metric: useful matrix-profile cell updates per second, cells = L(L+1)/2, L = (n-m+1) - m/4.
-Workload (config.workload): BASELINE.json configs[1] -- double, n = 1048576, m = 256 on a
-data/binary/1048576.tsb-shaped synthetic series (i.i.d. U[0,1) float64), fixed total work whatever the
-GPU count ("strong" scaling: the diagonal bands are dealt round-robin over the ranks and the per-rank
-profiles are max-merged over NCCL).
+Workload (config.workload): double, n = 1048576, m = 256 on a synthetic RANDOM WALK (BASELINE.json north_star: "throughput on
+synthetic random-walk series of the named n and m"), fixed total work whatever the GPU count ("strong" scaling: the diagonal
+bands are dealt round-robin over the ranks and the per-rank profiles are max-merged over NCCL inside libmpb200.so).
+The tsb-shaped series of BASELINE.json configs[1] (i.i.d. U[0,1), what the reference's data/binary/*.tsb hold) is measured in
+the same run with the same steps and reported as a full second block, `tsb_shaped`.
 
-A step = one whole matrix profile: precompute kernel + diagonal-band kernel [+ NCCL merge] + finalize.
+A step = one whole matrix profile in the default (chain-faithful) fp64 mode: precompute kernels + diagonal-band kernel
++ chain-carry resolve [+ NCCL merges] + finalize.
   value  : series already resident in HBM when the step starts (device time, CUDA events, max over ranks)
-  e2e    : the same through the C ABI's one-call host-buffer entry (mpb_compute / plan upload+download):
-           pinned host series -> H2D -> kernels -> D2H of profile + index, every step.
-  roofline: the diagonal-band kernel against the FP64 pipe issue peak measured in this run (DFMA
-           microbenchmark), 4 FP64-pipe ops per useful cell; HBM traffic is
-           reported beside it as evidence that HBM is not the limiter.
-  cpu_baseline / --impl reference: the reference's own Vanilla kernel sources (oracle/_ref, compiled
-           from /root/reference at build time) on the host cores, on a bounded sample of diagonal chunks.
+  e2e    : the same through the C ABI with HOST buffers: pinned host series -> H2D -> kernels -> D2H of profile + index, every
+           step; `one_call_ms` is mpb_compute() itself (pageable buffers, plan create/destroy inside) timed once on the host clock
+  roofline: the diagonal-band kernel against the FP64 pipe issue peak measured in this run (DFMA microbenchmark).
+           `frac` follows SURVEY.md section 8-d (4 pipe ops per useful cell: the reference formulation's 2 DFMA + 2 DMUL);
+           `frac_physical` counts what the kernel EXECUTES, from its own counters (cells walked, blocks replayed, cells parked,
+           diagonals re-seeded, sketch) -- the filter never forms P in its hot loop, so this is about half of `frac`.
+  cpu_baseline / --impl reference: the reference's own Vanilla kernel sources (oracle/_ref, compiled from /root/reference at build
+           time) on the host cores, on a bounded sample of diagonal chunks -- the SAME chunks in both legs for a given thread count.
 """
 import argparse
 import json
@@ -30,8 +33,8 @@ sys.path.insert(0, os.path.join(ROOT, "matrix-profile-hls_b200", "python"))
 
 METRIC = "matrix-profile cell updates/sec"
 UNIT = "cells/s"
-_CAL = {}
-REF_W = 4096          # MP_SIZE_W of the reference's README configuration (README.md:35)
+REF_W = 4096              # MP_SIZE_W of the reference's README configuration (README.md:35)
+REF_NOMINAL_RATE = 1.6e8  # useful cells/s of one host thread running the reference's Vanilla kernel: sizes the sample
 
 
 def synth_series(n, kind, seed=1234):
@@ -46,11 +49,10 @@ def useful_cells(n, m):
 
 
 def chunk_useful_cells(n, m, w, it):
-    """Useful cells of diagonal chunk `it` (diagonals [it*w, (it+1)*w), exclusion zone and the
-    out-of-range triangle removed)."""
+    """Useful cells of diagonal chunk `it` (diagonals [it*w, (it+1)*w), exclusion zone and the out-of-range triangle removed)."""
     sublen, excl = n - m + 1, m // 4
     lo, hi = max(it * w, excl), min((it + 1) * w, sublen)
-    return sum(sublen - d for d in range(lo, hi)) if hi > lo else 0
+    return (hi - lo) * (2 * sublen - lo - hi + 1) // 2 if hi > lo else 0
 
 
 class ClockSampler:
@@ -97,24 +99,27 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # CPU baseline: the reference's own kernel sources on the host cores (bounded sample of chunks)
 # --------------------------------------------------------------------------------------------------
-def cpu_reference_sample(n, m, kind, target_s=15.0, threads=None, est_rate=None):
-    """Times the reference's Vanilla kernel (kernel/MatrixProfileKernelVanilla.cpp, compiled unmodified into
-    oracle/_ref/libmpref_fast.so with -O3 -march=native; falls back to the C restatement when the reference
-    was not compiled here) on one diagonal chunk of width w = 4096 per host thread, chunks chosen so that
-    each costs about target_s seconds.  Returns the cpu_baseline object."""
-    import numpy as np
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))      # the oracle: bench's cpu_baseline leg may execute it
-    from concurrent.futures import ThreadPoolExecutor
-    from oracle_py import Oracle, RefShim
-    threads = threads or os.cpu_count() or 1
+def reference_sample_chunks(n, m, threads, target_s):
+    """The diagonal chunks (width w) the CPU legs time: one per host thread, consecutive, placed where a chunk costs about
+    target_s seconds at the nominal per-thread rate -- a pure function of (n, m, threads, target_s), so the cpu_baseline leg and
+    the --impl reference arm time the same sample."""
     sublen = n - m + 1
     w = REF_W if n >= 4 * REF_W else 256
     nit = (n - m + w) // w
-    if est_rate is None:
-        est_rate = _CAL.get("rate", 2.0e8)             # cells/s per thread; refined after every sample
-    want_rows = max(w, int(target_s * est_rate / w))
+    want_rows = max(w, int(target_s * REF_NOMINAL_RATE / w))
     it0 = max(0, min(nit - threads, (sublen - want_rows) // w))
-    its = [it for it in range(it0, min(nit, it0 + threads))]
+    return w, nit, list(range(it0, min(nit, it0 + threads)))
+
+
+def cpu_reference_sample(n, m, kind, target_s=12.0, threads=None):
+    """Times the reference's Vanilla kernel (kernel/MatrixProfileKernelVanilla.cpp, compiled unmodified into
+    oracle/_ref/libmpref_fast.so with -O3 -march=native; the C restatement when the reference was not compiled here) on one
+    diagonal chunk per host thread.  Returns the cpu_baseline object."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))      # the oracle: bench's CPU legs may execute it
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle_py import Oracle, RefShim
+    threads = threads or os.cpu_count() or 1
+    w, nit, its = reference_sample_chunks(n, m, threads, target_s)
     T = synth_series(n, kind)
     orc = Oracle(fast=True)
     inp = orc.precompute(T, m)
@@ -129,9 +134,8 @@ def cpu_reference_sample(n, m, kind, target_s=15.0, threads=None, est_rate=None)
         list(ex.map(one, its))
     dt = time.perf_counter() - t0
     cells = sum(chunk_useful_cells(n, m, w, it) for it in its)
-    _CAL["rate"] = cells / dt / len(its)
     return {"value": cells / dt, "unit": UNIT, "cores": len(its), "kind": "reference" if use_ref else "port",
-            "sample": f"Vanilla kernel, double, w={w}: diagonal chunks {its[0]}..{its[-1]} of {nit} of the same n={n}, m={m} series, "
+            "sample": f"Vanilla kernel, double, w={w}: diagonal chunks {its[0]}..{its[-1]} of {nit} of the same n={n}, m={m} {kind} series, "
                       f"one chunk per host thread, {cells:.4g} useful cells in {dt:.1f} s (-O3 -march=native)",
             "seconds": dt}
 
@@ -141,10 +145,9 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     vals = []
-    base = None
     for i in range(args.warmup + args.steps):
         # warm-up steps are short samples (page the library and the series in); timed ones are the bounded sample
-        base = cpu_reference_sample(args.n, args.m, args.data, target_s=2.0 if i < args.warmup else args.ref_seconds)
+        base = cpu_reference_sample(args.n, args.m, args.data, target_s=1.0 if i < args.warmup else args.ref_seconds)
         if i >= args.warmup:
             vals.append(base)
     cells_s = sum(b["value"] * b["seconds"] for b in vals) / sum(b["seconds"] for b in vals)
@@ -152,17 +155,27 @@ def run_reference_arm(args):
     base = dict(vals[-1]); base["value"] = cells_s
     line = {"impl": "reference", "metric": METRIC, "value": cells_s, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args), "cpu_baseline": base,
+            "config": workload_config(args, args.data), "cpu_baseline": base,
             "e2e": {"value": cells_s, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
 
 
-def workload_config(args):
-    return {"workload": f"Tiled-kernel config, {'double' if args.dtype == 'f64' else 'float'}, n={args.n}, m={args.m}, "
-                        f"{'tsb-shaped U[0,1)' if args.data == 'uniform' else 'random-walk'} synthetic series (BASELINE.json configs[1])",
-            "n": args.n, "m": args.m, "series": args.data, "partition": f"diagonal bands round-robin over {args.gpus} GPU(s)",
+def workload_config(args, kind):
+    series = "random-walk (north_star)" if kind == "walk" else "tsb-shaped U[0,1) (BASELINE.json configs[1])"
+    return {"workload": f"matrix profile, {'double' if args.dtype == 'f64' else 'float'}, n={args.n}, m={args.m}, synthetic {series} series, "
+                        f"default mode ({'chain-faithful: running mean + telescoped chain carry' if args.dtype == 'f64' else 'periodic exact QT re-seed'})",
+            "n": args.n, "m": args.m, "series": kind, "partition": f"diagonal bands round-robin over {args.gpus} GPU(s), NCCL max-merge in libmpb200.so",
             "l2": "flushed between timed steps (256 MiB write)"}
+
+
+def executed_pipe_ops(tm, m, sketch_cells):
+    """FP64/FP32-pipe operations the step EXECUTES, from the kernel's own counters:
+    hot loop 128 FMA + 2 MUL per 64-cell block of every walked cell; a replayed block (8 rows x 8 diagonals x 32 lanes) walks its
+    2048 cells again with 2 FMA + 2 MUL each; a parked cell costs 2 MUL in the drain; a re-seeded diagonal m FMA; a sketched cell
+    2 FMA + 2 MUL."""
+    return (tm["cells_walked"] * (130.0 / 64.0) + tm["replays"] * 2048 * 4.0 + tm["filter_hits"] * 8 * 2.0
+            + tm["reseeded_diagonals"] * float(m) + sketch_cells * 4.0)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -192,22 +205,17 @@ def run_gpu_arm(args):
     stream = torch.cuda.ExternalStream(ctx.stream, device=local)
     plan = mp.Plan(ctx, n, m, dtype, 0)
     plan.set_shard(rank, world)
-    T_pinned = torch.from_numpy(synth_series(n, args.data)).pin_memory()
     MP_pinned = torch.empty(sublen, dtype=torch.float64).pin_memory()
     MPI_pinned = torch.empty(sublen, dtype=torch.int32).pin_memory()
-    plan.upload_series_ptr(T_pinned.data_ptr())
-    ctx.finish()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB of L2
-    corr_buf = torch.empty(sublen, dtype=torch.float64, device="cuda")
-    index_buf = torch.empty(sublen, dtype=torch.int32, device="cuda")
+    comm = None
     if world > 1:
-        from mpb200.dist import compute_merged
-        with torch.cuda.stream(stream):
-            dist.all_reduce(index_buf)          # communicator creation stays outside the timed region
+        from mpb200.dist import make_comm
+        comm = make_comm(ctx)               # communicator creation stays outside the timed region
         ctx.finish()
 
-    def step(e2e):
-        """One whole matrix profile on this rank's band shard; returns (t0, t1, launches) events on the engine stream."""
+    def step(e2e, T_pinned):
+        """One whole matrix profile on this rank's band shard; returns (t0, t1) events on the engine stream."""
         with torch.cuda.stream(stream):
             flush.zero_()
             t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
@@ -215,32 +223,31 @@ def run_gpu_arm(args):
             if e2e:
                 plan.upload_series_ptr(T_pinned.data_ptr())
             plan.precompute()
-            extra = 0
             if world > 1:
-                extra = compute_merged(plan, corr_buf, index_buf, world)   # first bands, merge, remaining bands, merge
+                plan.compute_merged(comm)   # shared sketch, first bands, threshold merge, remaining bands, result merge (csrc/multi_gpu.cu)
             else:
                 plan.compute()
             plan.finalize()
             if e2e:
                 plan.download_into(MP_pinned.data_ptr(), MPI_pinned.data_ptr())
             t1.record(stream)
-        return t0, t1, extra
+        return t0, t1
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(e2e, steps, warmup):
+    def timed(e2e, steps, warmup, T_pinned):
         for _ in range(warmup):
-            step(e2e)
+            step(e2e, T_pinned)
         sync_all()
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
-        evs, kern_ms, launches = [], [], 0
+        evs, kern_ms, launches, tm = [], [], 0, None
         for _ in range(steps):
-            t0, t1, extra = step(e2e)
+            t0, t1 = step(e2e, T_pinned)
             torch.cuda.synchronize()
             tm = plan.timings()
             kern_ms.append(tm["compute_ms"])
@@ -255,54 +262,73 @@ def run_gpu_arm(args):
             dist.all_reduce(total, op=dist.ReduceOp.MAX)
         return total.item() / steps, sum(kern_ms) / len(kern_ms), launches, clocks, tm
 
-    ms_dev, band_ms, launches, clocks, tm = timed(False, args.steps, args.warmup)
-    ms_e2e, _, _, _, _ = timed(True, args.steps, max(1, args.warmup // 2))
-    # Secondary workload, reported beside the headline (not the headline): the same n and m on a random walk
-    # (BASELINE.json north_star / configs[2..3]); smooth series keep far more cells near the running best.
-    other = "walk" if args.data == "uniform" else "uniform"
-    T_other = torch.from_numpy(synth_series(n, other)).pin_memory()
-    plan.upload_series_ptr(T_other.data_ptr())
-    ctx.finish()
-    ms_other, band_other, _, _, tm_other = timed(False, max(2, args.steps // 2), 1)
-    plan.upload_series_ptr(T_pinned.data_ptr())
-    ctx.finish()
-
     fma_peak, _ = ctx.measure_fma_peak(dtype, 1 << 15)
     fma_peak, _ = ctx.measure_fma_peak(dtype, 1 << 16)
-    out = None
-    if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except OSError:
-            pass
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+
+    def measure(kind):
+        T_pinned = torch.from_numpy(synth_series(n, kind)).pin_memory()
+        plan.upload_series_ptr(T_pinned.data_ptr())
+        ctx.finish()
+        ms_dev, band_ms, launches, clocks, tm = timed(False, args.steps, args.warmup, T_pinned)
+        ms_e2e, _, _, clocks_e2e, _ = timed(True, args.steps, max(3, args.warmup // 2), T_pinned)
+        plan.check()                                        # every rank: the chain-carry margin covered what it had to (raises otherwise)
+        one_call_ms = None
+        if world == 1 and rank == 0:                        # mpb_compute itself: pageable host buffers, plan create / destroy inside
+            Tn = T_pinned.numpy().copy()
+            mp.matrix_profile(Tn, m, dtype, 0, ctx=ctx)     # first call pays the allocator's page faults
+            t0 = time.perf_counter()
+            mp.matrix_profile(Tn, m, dtype, 0, ctx=ctx)
+            one_call_ms = (time.perf_counter() - t0) * 1e3
+        if rank != 0:
+            return None
         my_cells = cells / world                                   # round-robin bands: equal shares to within one band
         ops = 4.0 * my_cells / (band_ms * 1e-3)
-        prof_path = os.path.join(ROOT, "profiles", "tile_kernel_traffic.json")
-        traffic = None
-        if os.path.exists(prof_path):
-            traffic = json.load(open(prof_path)).get(f"{args.dtype}_n{n}_m{m}")
+        sketch_cells = (sublen - m // 4) * 512.0 / world if dtype == mp.F64 or world == 1 else (sublen - m // 4) * 512.0
+        executed = executed_pipe_ops(tm, m, sketch_cells)
         hbm_alg = 8.0 * n + 12.0 * sublen                          # read T once, write MP + MPI once
-        out = {"metric": METRIC, "value": cells / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-               "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
-               "data": "synthetic", "config": workload_config(args),
-               "e2e": {"value": cells / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 12 * sublen},
-               "gpu_launches": launches,
-               "roofline": {"bound": "fp64_fma_pipe" if args.dtype == "f64" else "fp32_fma_pipe", "kernel": "tile_kernel",
-                            "achieved": ops / 1e12, "peak": fma_peak / 1e12, "unit": "T pipe-ops/s (4 per cell: 2 FMA + 2 MUL)",
-                            "frac": ops / fma_peak, "peak_source": "DFMA/FFMA issue-rate microbenchmark measured in this run (mpb_measure_fma_peak)",
-                            "kernel_ms": band_ms, "kernel_share_of_step": band_ms / ms_dev, "traffic": traffic,
-                            "hbm": {"algorithmic_bytes_per_step": hbm_alg, "achieved_gbs": hbm_alg / (band_ms * 1e-3) / 1e9,
-                                    "peak_gbs": peaks.get("hbm_gbs", 6650.0), "peak_source": "measured" if peaks else "fallback"}},
-               "clocks": clocks, "phases_ms": {k: tm[k] for k in ("precompute_ms", "compute_ms", "finalize_ms")},
-               "slow_updates": tm["slow_updates"], "filter_hits": tm["filter_hits"], "replays": tm["replays"], "bands_rank0": tm["bands"],
-               "secondary": {"series": other, "value": cells / (ms_other * 1e-3), "unit": UNIT, "ms_per_step": ms_other,
-                             "roofline_frac": 4.0 * my_cells / (band_other * 1e-3) / fma_peak, "slow_updates": tm_other["slow_updates"],
-                             "filter_hits": tm_other["filter_hits"], "replays": tm_other["replays"]}}
-        out["roofline"]["executed_pipe_ops_per_cell"] = 2.03     # 2 DFMA per cell + 2 DMUL per 64-cell block (the filter never forms P)
+        traffic = None
+        prof_path = os.path.join(ROOT, "profiles", "tile_kernel_traffic.json")
+        if world == 1 and os.path.exists(prof_path):              # a 1-GPU ncu figure: not repeated for sharded runs
+            traffic = json.load(open(prof_path)).get(f"{args.dtype}_n{n}_m{m}_{kind}")
+        return {"value": cells / (ms_dev * 1e-3), "ms_per_step": ms_dev,
+                "e2e": {"value": cells / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 12 * sublen,
+                        "one_call_ms": one_call_ms, "clocks": clocks_e2e},
+                "gpu_launches": launches,
+                "roofline": {"bound": "fp64_fma_pipe" if args.dtype == "f64" else "fp32_fma_pipe", "kernel": "tile_kernel (+ chain-carry scan / resolve, sketch)",
+                             "achieved": ops / 1e12, "peak": fma_peak / 1e12, "unit": "T pipe-ops/s (4 per cell: 2 FMA + 2 MUL)",
+                             "frac": ops / fma_peak, "peak_source": "DFMA/FFMA issue-rate microbenchmark measured in this run (mpb_measure_fma_peak)",
+                             "executed_pipe_ops_per_cell": executed / my_cells, "frac_physical": executed / (band_ms * 1e-3) / fma_peak,
+                             "executed_source": "kernel counters of rank 0: cells walked, blocks replayed, cells parked, diagonals re-seeded, sketch",
+                             "kernel_ms": band_ms, "kernel_share_of_step": band_ms / ms_dev, "traffic": traffic,
+                             "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one 1-GPU ncu --set full capture (profiles/)" if traffic else None,
+                             "hbm": {"algorithmic_bytes_per_step": hbm_alg, "achieved_gbs": hbm_alg / (band_ms * 1e-3) / 1e9,
+                                     "peak_gbs": peaks.get("hbm_gbs", 6650.0), "peak_source": "measured" if peaks else "fallback"}},
+                "clocks": clocks, "phases_ms": {k: tm[k] for k in ("precompute_ms", "compute_ms", "finalize_ms")},
+                "counters": {k: tm[k] for k in ("slow_updates", "filter_hits", "replays", "cells_walked", "reseeded_diagonals", "chain_candidates",
+                                                "chain_max_correction", "chain_bound", "chain_margin", "items", "segment_rows", "bands")}}
+
+    head = measure(args.data)
+    other = "uniform" if args.data == "walk" else "walk"
+    second = measure(other) if not args.no_second_series else None
+    out = None
+    if rank == 0:
+        out = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
+               "data": "synthetic", "config": workload_config(args, args.data)}
+        out.update({k: head[k] for k in ("e2e", "gpu_launches", "roofline", "clocks", "phases_ms", "counters")})
+        if second:
+            second["config"] = workload_config(args, other)
+            out["tsb_shaped" if other == "uniform" else "random_walk"] = second
     plan.close()
+    if comm is not None:
+        comm.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_reference_sample(n, m, args.data, target_s=1.5)          # calibrates the per-thread rate (untimed warm-up)
+        cpu_reference_sample(n, m, args.data, target_s=1.0)          # pages the library and the series in (untimed)
         cb = cpu_reference_sample(n, m, args.data, target_s=args.ref_seconds)
         cb.pop("seconds", None)
         out["cpu_baseline"] = cb
@@ -323,9 +349,10 @@ def main():
     ap.add_argument("--n", type=int, default=1 << 20)
     ap.add_argument("--m", type=int, default=256)
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
-    ap.add_argument("--data", default="uniform", choices=["uniform", "walk"])
+    ap.add_argument("--data", default="walk", choices=["uniform", "walk"])
     ap.add_argument("--ref-seconds", type=float, default=12.0, help="CPU seconds per reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-second-series", action="store_true", help="skip the second series block (long configs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -27,6 +27,8 @@ extern "C" {
 #define MPB_E_NO_DEVICE (-2)  /* no usable CUDA device: there is no CPU fallback */
 #define MPB_E_CUDA (-3)       /* CUDA runtime failure (the reference's RuntimeError, OpenCL.hpp:54-60) */
 #define MPB_E_NOMEM (-4)
+#define MPB_E_MARGIN (-5)     /* chain-carry mode: the corrections found exceed what the near-tie margin covers; the result was not
+                                 proven -- run again with a wider margin (mpb_plan_set_chain_margin; mpb_compute does so itself) */
 
 /* MP_DATA_TYPE (CMakeLists.txt:35-37) */
 #define MPB_F64 0
@@ -54,6 +56,8 @@ typedef struct mpb_context mpb_context; /* replaces OpenCL::Context   (OpenCL.hp
 typedef struct mpb_buffer mpb_buffer;   /* replaces OpenCL::Buffer<T> (OpenCL.hpp:109-211) */
 typedef struct mpb_plan mpb_plan;       /* whole-problem engine state (no reference equivalent: the
                                            reference sizes everything at configure time) */
+typedef struct mpb_comm mpb_comm;       /* one rank of a multi-GPU job: an NCCL communicator bound to a context (replaces the
+                                           replication over MP_KERNEL_REPL compute units, host/MatrixProfileHost.cpp:78-97) */
 
 const char *mpb_last_error(void);
 const char *mpb_version(void);
@@ -116,6 +120,8 @@ typedef struct {
                                     independent segments were from the unbroken chain); 0 in the other modes */
     double chain_bound;          /* chain-carry mode: upper bound of the ABSOLUTE correction any cell's P could receive */
     double chain_margin;         /* chain-carry mode: the near-tie margin in effect (relative) */
+    int64_t cells_walked;        /* cells this rank's tile kernel walks (useful cells + exclusion-free padding of the last tiles / bands) */
+    int64_t reseeded_diagonals;  /* (diagonal, segment) pairs that start from an exact dot product of m terms */
 } mpb_timings;
 
 /* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised
@@ -173,11 +179,47 @@ void *mpb_plan_mp_device_ptr(mpb_plan *plan);                       /* double[n-
 void *mpb_plan_mpi_device_ptr(mpb_plan *plan);                      /* int32[n-m+1] */
 /* The precomputed InputDataPack[n-m+1] (reference layout), for parity checks of kernel (1). */
 int mpb_plan_download_input(mpb_plan *plan, void *input_host);
+/* Waits for the plan's work and reports what only the device knows: MPB_E_NOMEM if the near-tie log overflowed,
+ * MPB_E_MARGIN if the chain-carry corrections exceed what the margin covers (mpb_plan_download runs the same check). */
+int mpb_plan_check(mpb_plan *plan);
 int mpb_plan_timings(mpb_plan *plan, mpb_timings *out);
 /* After mpb_plan_precompute with the reference's running mean: *walked = 1 when the chain was walked element by element
  * (MPB_FLAG_MU_WALK, or the verified segmented-scan formulation failed a check and fell back), 0 when the scan stood. */
 int mpb_plan_mu_walked(mpb_plan *plan, int *walked);
 int64_t mpb_useful_cells(int n, int m);
+
+/* ---- multi-GPU: diagonal bands round-robin over the ranks, profiles max-merged over NVLink with NCCL
+ *      (the reference: chunk k on compute unit k % MP_KERNEL_REPL, host-side UpdateAggregates;
+ *      host/MatrixProfileHost.cpp:101-137, include/host/HostSideComputation.hpp:72-90).
+ *      NCCL is bound at run time (libnccl.so.2); single-GPU use needs none. ---- */
+#define MPB_COMM_ID_BYTES 128
+/* ncclGetUniqueId: call on one rank, hand the 128 bytes to all ranks (MPI, torch.distributed, a file ...). */
+int mpb_comm_unique_id(void *id, size_t bytes);
+/* ncclCommInitRank on ctx's device.  Collective: every rank of the job must call it. */
+int mpb_comm_create(mpb_context *ctx, const void *id, int rank, int world, mpb_comm **comm);
+int mpb_comm_destroy(mpb_comm *comm);
+int mpb_comm_rank(mpb_comm *comm);
+int mpb_comm_world(mpb_comm *comm);
+/* Exact (corr, index) max of the ranks' profiles, in place, stream-ordered: ncclAllReduce MAX on the correlations' int64 bit
+ * patterns, then MIN on the indices of the ranks that hold the maximum (ties -> smallest index).  Addresses the result
+ * profile, or the filter thresholds after mpb_plan_merge_select(plan, 1). */
+int mpb_plan_allreduce(mpb_plan *plan, mpb_comm *comm);
+/* One rank's compute step of a multi-GPU job (after mpb_plan_set_shard(rank, world) and mpb_plan_precompute): shared sketch
+ * of band 0 (each rank walks 1/world of its rows; one max-reduction), the first bands, max-merge of the thresholds, the
+ * remaining bands, max-merge of the result.  Every rank then holds the job's profile; call mpb_plan_finalize on any. */
+int mpb_plan_compute_merged(mpb_plan *plan, mpb_comm *comm);
+int mpb_merge_point(int total_bands, int world);   /* local bands walked before the threshold merge (0 = no early merge) */
+int mpb_plan_total_bands(mpb_plan *plan, int *count);   /* diagonal bands of the whole problem (all ranks) */
+/* Pieces of the shared sketch, for callers that bring their own collective: this rank's share of band `band` into hint[]
+ * (int32[mpb_plan_hint_count], max-reduce it across the sharing ranks), then mpb_plan_apply_hint. */
+int mpb_plan_sketch_share(mpb_plan *plan, int band, int share_rank, int share_world);
+void *mpb_plan_hint_device_ptr(mpb_plan *plan);
+int mpb_plan_hint_count(mpb_plan *plan);
+int mpb_plan_apply_hint(mpb_plan *plan);
+/* One call, ngpus GPUs of this process (devices[] or 0..ngpus-1), HOST buffers: one host thread per GPU, NCCL merge, rank 0
+ * writes MP / MPI.  timings (may be NULL) receives ngpus entries.  What MatrixProfileHost --gpus G runs. */
+int mpb_compute_multi(int ngpus, const int *devices, const double *T, int n, int m, int dtype, unsigned flags,
+                      double *MP, int32_t *MPI, mpb_timings *timings);
 
 /* ---- measurement support ---- */
 /* Register-resident DFMA (dtype MPB_F64) / FFMA (MPB_F32) issue-rate microbenchmark on ctx's device:

@@ -39,6 +39,7 @@ struct TileLaunch {
     int item_begin;                     // first work item of this launch (index into the prefix table)
     unsigned long long *counters;       // device: [0] cells parked, [1] profile slots improved, [2] blocks replayed (may be null)
     int sketch_band = -1, sketch_seg_rows = 0;   // sketch launches only: walk this one band in segments of sketch_seg_rows rows (own cut; -1 / 0 = the items of the table)
+    int sketch_share_rank = 0, sketch_share_world = 1;   // one-band sketch shared by a multi-GPU job: this launch walks segments rank, rank + world, ...
     ChainFix chain = {};                // chain-carry mode (fp64, re-seeded segments): log != nullptr switches it on
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
@@ -55,8 +56,10 @@ cudaError_t launch_chain_resolve(const TileLaunch &p, int lb_begin, int lb_end, 
                                  unsigned long long *stats, cudaStream_t s);
 
 // sketch pass over the items of `p` (first bands of a step): hint[np] <- high words of per-slot lower bounds, then borrowed entries into prof
-cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
-cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
+// apply = false: leave hint[] for a max-reduction across the ranks that share the sketch, then launch_apply_hint
+cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s);
+cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s);
+cudaError_t launch_apply_hint(const int *hint, ProfileEntry *prof, int sublen, cudaStream_t s);
 
 // kernel (3): merge.cu
 cudaError_t launch_finalize(const ProfileEntry *prof, int sublen, int m, double *MP, int32_t *MPI, double *corr, cudaStream_t s);

@@ -1,9 +1,7 @@
 // runtime.cu -- implementation of the C ABI in include/mp_b200.h over the CUDA runtime.
 // Replaces the reference's OpenCL/XRT wrapper include/host/OpenCL.hpp (Context / Buffer / Program /
 // Kernel) and hosts the whole-problem engine (plan) that drives kernels (1)-(3).
-#include "../../include/mp_b200.h"
-#include "mp_common.cuh"
-#include "mp_kernels.h"
+#include "mp_runtime.h"
 
 #include <algorithm>
 #include <cmath>
@@ -35,76 +33,15 @@ int fma_peak_threads();
 
 namespace {
 thread_local char g_err[512] = "";
+}  // namespace
 
-int fail(int code, const char *fmt, ...) {
+int mpb_fail(int code, const char *fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof g_err, fmt, ap);
     va_end(ap);
     return code;
 }
-#define CU(expr)                                                                                     \
-    do {                                                                                             \
-        cudaError_t e__ = (expr);                                                                    \
-        if (e__ != cudaSuccess)                                                                      \
-            return fail(e__ == cudaErrorMemoryAllocation ? MPB_E_NOMEM : MPB_E_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
-    } while (0)
-}  // namespace
-
-struct mpb_context {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t mark = nullptr, now = nullptr;   // Finish() reports device time since the last Finish()
-    void *tlf_scratch = nullptr;
-    size_t tlf_scratch_bytes = 0;
-    int sm_count = 0;
-};
-
-struct mpb_buffer {
-    mpb_context *ctx = nullptr;
-    void *ptr = nullptr;
-    size_t bytes = 0;
-};
-
-struct mpb_plan {
-    mpb_context *ctx = nullptr;
-    int n = 0, m = 0, sublen = 0, excl = 0, np = 0, dtype = MPB_F64;
-    unsigned flags = 0;
-    int rank = 0, world = 1;
-    double *T = nullptr, *mu = nullptr;
-    void *df_dg = nullptr, *inv = nullptr, *qt0 = nullptr;    // data_t arrays, zero-padded to np
-    void *nm = nullptr, *mnc = nullptr;                       // data_t {norm, inv} pairs and window-min norms, np entries
-    mpb::ProfileEntry *prof = nullptr;                        // np slots: running bests = the tile kernel's filter thresholds
-    mpb::ProfileEntry *fin = nullptr;                         // np slots: the result profile of the chain-carry mode (else unused; the result is prof)
-    bool seq_mean = false, chain_fix = false;                 // mu by the reference's running recurrence; telescoped chain carry (mp_common.cuh)
-    bool merge_thresholds = false;                            // export / import / merge_peers address prof even in the chain-carry mode
-    double *seg_seed = nullptr, *seg_end = nullptr;           // chain carry: S_k / E_k of the work items of one launch chunk, [chunk_items][BAND_W]
-    long long chunk_items = 0;                                // capacity of those arrays in work items
-    mpb::ChainLogEntry *chain_log = nullptr;                  // LOG_SHARDS sub-logs of log_shard_cap candidates
-    unsigned long long *log_count = nullptr;                  // LOG_SHARDS counters, one per 128-byte line
-    unsigned long long *chain_stats = nullptr;                // [0] largest relative correction (double bits) [1] candidates resolved [2] log overflow seen
-    unsigned log_shard_cap = 0;
-    long long log_entries_req = -1;                           // requested total log capacity (-1 = automatic)
-    double *inv_blockmax = nullptr;                           // largest inv per block of seg_rows rows (bound of the chain-carry corrections)
-    int inv_blocks = 0;
-    int margin_log2 = 17;                                     // near-tie margin = 2^-margin_log2
-    double *MP = nullptr, *corr = nullptr;
-    int32_t *MPI = nullptr;
-    unsigned long long *slow_counter = nullptr;
-    void *mu_scratch = nullptr;           // work space of the parallel running-mean kernels (seq_mean only)
-    int *hint = nullptr;                  // np high words: lower bounds of the slots' best correlation from the sketch pass
-    int sketch_bands = -1;                // local bands the sketch pass covers (-1 = default, 0 = off)
-    int seg_rows = -1;                    // requested (-1 = auto)
-    int seg_rows_eff = 0;                 // in effect for the current table
-    int *item_start = nullptr;            // device prefix table of work items
-    int nlb = 0;
-    long long items = 0;
-    bool table_dirty = true;
-    std::vector<int> table_host;          // host copy of the work-item table (prefix sums, then band ids)
-    cudaEvent_t ev[8] = {};
-    mpb_timings tm = {};
-    bool ran_h2d = false;
-};
 
 // Live-handle registry: destroying a context destroys the plans and buffers created on it first, and destroying a
 // handle twice (or after its context went away) is a no-op -- language bindings finalise objects in any order.
@@ -402,6 +339,17 @@ static int plan_build_table(mpb_plan *p) {
     CU(cudaMemcpy(p->item_start, tab.data(), sizeof(int) * tab.size(), cudaMemcpyHostToDevice));
     p->table_host = tab;
     p->nlb = ((int)tab.size() - 1) / 2; p->items = items; p->seg_rows_eff = seg; p->table_dirty = false;
+    {   // cells the tile kernel walks for this rank: every warp (WARP_DIAGS diagonals) runs whole tiles of TILE_H rows down its longest diagonal
+        long long walked = 0, seeded = 0;
+        for (int lb = 0; lb < p->nlb; ++lb)
+            for (int w = 0; w < mpb::BAND_WARPS; ++w) {
+                const long long rows = (long long)p->sublen - (p->excl + (long long)tab[(size_t)p->nlb + 1 + lb] * mpb::BAND_W + w * mpb::WARP_DIAGS);
+                if (rows <= 0) continue;
+                walked += (rows + mpb::TILE_H - 1) / mpb::TILE_H * mpb::TILE_H * mpb::WARP_DIAGS;
+                if (seg > 0) seeded += ((rows + seg - 1) / seg - 1) * mpb::WARP_DIAGS;
+            }
+        p->tm.cells_walked = walked; p->tm.reseeded_diagonals = seeded;
+    }
     if (p->chain_fix && seg == 0) p->chain_fix = false;          // segment length forced to 0: full-length chains, nothing to carry
     if (p->chain_fix) {
         // S_k / E_k arrays: one launch chunk at a time (whole bands; at least the longest band), at most MPB_CHAIN_CHUNK_ITEMS items
@@ -479,6 +427,7 @@ int mpb_plan_precompute(mpb_plan *p) {
         p->tm.launches += 1;
     }
     CU(cudaEventRecord(p->ev[3], s));
+    p->step_open = false; p->sketched = false;
     return MPB_OK;
 }
 
@@ -488,6 +437,55 @@ int mpb_plan_local_bands(mpb_plan *p, int *count) {
     int rc = plan_build_table(p);
     if (rc != MPB_OK) return rc;
     *count = p->nlb;
+    return MPB_OK;
+}
+
+// first launch of a step: statistics and the compute timer start here
+static int plan_step_begin(mpb_plan *p) {
+    if (p->step_open) return MPB_OK;
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
+    CU(cudaEventRecord(p->ev[4], s));
+    p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
+    p->step_open = true;
+    return MPB_OK;
+}
+static bool plan_sketch_allowed(const mpb_plan *p) { return !(p->flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_SEED | MPB_FLAG_NO_RESEED)); }
+
+int mpb_plan_total_bands(mpb_plan *p, int *count) {
+    if (!p || !count) return fail(MPB_E_INVALID, "null argument");
+    *count = mpb::band_count(p->sublen, p->excl);
+    return MPB_OK;
+}
+
+// One-band sketch shared by the ranks of a multi-GPU job: this rank walks segments share_rank, share_rank + share_world, ... of
+// global band `band` and leaves the high words in hint[]; the caller max-reduces hint[] across the ranks, then mpb_plan_apply_hint.
+int mpb_plan_sketch_share(mpb_plan *p, int band, int share_rank, int share_world) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    if (share_world < 1 || share_rank < 0 || share_rank >= share_world || band < 0 || band >= mpb::band_count(p->sublen, p->excl)) return fail(MPB_E_INVALID, "bad sketch share");
+    if (p->dtype != MPB_F64 || !plan_sketch_allowed(p)) return fail(MPB_E_INVALID, "the shared sketch is for the fp64 re-seeded modes");
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaSetDevice(p->ctx->device));
+    int rc = plan_build_table(p);
+    if (rc == MPB_OK) rc = plan_step_begin(p);
+    if (rc != MPB_OK) return rc;
+    mpb::TileLaunch sl;
+    sl.n = p->n; sl.m = p->m; sl.sublen = p->sublen; sl.excl = p->excl; sl.rank = p->rank; sl.world = p->world;
+    sl.seg_rows = p->seg_rows_eff; sl.strict = false; sl.series = p->T; sl.mu = p->mu; sl.item_start = p->item_start; sl.nlb = p->nlb;
+    sl.item_begin = 0; sl.items = 1; sl.counters = nullptr;
+    sl.sketch_band = band; sl.sketch_seg_rows = MPB_SKETCH_SEG_ROWS; sl.sketch_share_rank = share_rank; sl.sketch_share_world = share_world;
+    CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, false, s));
+    p->tm.launches += 1;
+    p->sketched = true;
+    return MPB_OK;
+}
+void *mpb_plan_hint_device_ptr(mpb_plan *p) { return p ? p->hint : nullptr; }
+int mpb_plan_hint_count(mpb_plan *p) { return p ? p->np : 0; }
+int mpb_plan_apply_hint(mpb_plan *p) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(mpb::launch_apply_hint(p->hint, p->prof, p->sublen, p->ctx->stream));
+    p->tm.launches += 1;
     return MPB_OK;
 }
 
@@ -509,14 +507,13 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
     tl.items = p->nlb > 0 ? (long long)p->table_host[lb_end] - tl.item_begin : 0;
     tl.counters = p->slow_counter;
     if (lb_begin == 0) {                      // first launch of a step: statistics and the compute timer start here
-        CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
-        CU(cudaEventRecord(p->ev[4], s));
-        p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
+        rc = plan_step_begin(p);
+        if (rc != MPB_OK) return rc;
         // Sketch pass over the first bands of this call (scamp_tile.cu): lower bounds for every slot, so that the tile
         // kernel meets a tight filter in the bands where the profile would still be empty.  Result-neutral; never in
         // the chain-faithful modes (their seg_rows = 0 makes a band a single item anyway).
         int sk = p->sketch_bands < 0 ? MPB_DEFAULT_SKETCH_BANDS : p->sketch_bands;
-        if (p->flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_SEED | MPB_FLAG_NO_RESEED)) sk = 0;
+        if (p->sketched || !plan_sketch_allowed(p)) sk = 0;
         if (sk > lb_end) sk = lb_end;
         if (sk > 0 && p->nlb > 0) {
             mpb::TileLaunch sl = tl;
@@ -529,9 +526,10 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
                 sl.sketch_band = p->table_host[(size_t)p->nlb + 1];
                 sl.sketch_seg_rows = MPB_SKETCH_SEG_ROWS;
             }
-            if (p->dtype == MPB_F64) CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, s));
-            else CU(mpb::launch_sketch_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->qt0, p->hint, p->prof, sl, s));
+            if (p->dtype == MPB_F64) CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, true, s));
+            else CU(mpb::launch_sketch_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->qt0, p->hint, p->prof, sl, true, s));
             p->tm.launches += sl.items > 0 ? 2 : 0;
+            p->sketched = true;
         }
     }
     if (p->chain_fix && tl.items > 0) {
@@ -657,9 +655,16 @@ static int chain_check(mpb_plan *p) {
     double bound; memcpy(&bound, &st[3], sizeof bound);
     const double margin = std::ldexp(1.0, -p->margin_log2);
     if (2.0 * bound > margin * MPB_CHAIN_FLOOR)      // two candidates further apart than the margin could have changed order
-        return fail(MPB_E_INVALID, "chain-carry corrections are bounded by %.3g, too large for the near-tie margin 2^-%d (needs 2 * bound <= margin / 64): "
-                                   "raise it with mpb_plan_set_chain_margin, or use MPB_FLAG_NO_RESEED", bound, p->margin_log2);
+        return fail(MPB_E_MARGIN, "chain-carry corrections are bounded by %.3g, too large for the near-tie margin 2^-%d (needs 2 * bound <= margin / 64): "
+                                  "widen it with mpb_plan_set_chain_margin, or use MPB_FLAG_NO_RESEED", bound, p->margin_log2);
     return MPB_OK;
+}
+
+int mpb_plan_check(mpb_plan *p) {
+    if (!p) return fail(MPB_E_INVALID, "plan is null");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaStreamSynchronize(p->ctx->stream));
+    return chain_check(p);
 }
 
 int mpb_plan_download(mpb_plan *p, double *MP_host, int32_t *MPI_host, double *corr_host) {
@@ -743,15 +748,21 @@ int mpb_plan_timings(mpb_plan *p, mpb_timings *out) {
 
 int mpb_compute(mpb_context *c, const double *T, int n, int m, int dtype, unsigned flags, double *MP, int32_t *MPI, mpb_timings *timings) {
     if (!c || !T || !MP || !MPI) return fail(MPB_E_INVALID, "null argument");
-    mpb_plan *p = nullptr;
-    int rc = mpb_plan_create(c, n, m, dtype, flags, &p);
-    if (rc == MPB_OK) rc = mpb_plan_upload_series(p, T);
-    if (rc == MPB_OK) rc = mpb_plan_precompute(p);
-    if (rc == MPB_OK) rc = mpb_plan_compute(p);
-    if (rc == MPB_OK) rc = mpb_plan_finalize(p);
-    if (rc == MPB_OK) rc = mpb_plan_download(p, MP, MPI, nullptr);
-    if (rc == MPB_OK && timings) rc = mpb_plan_timings(p, timings);
-    mpb_plan_destroy(p);
+    int rc = MPB_OK, margin = 0;
+    for (int attempt = 0; attempt < 4; ++attempt) {       // MPB_E_MARGIN: the same problem again with a 4x wider near-tie margin
+        mpb_plan *p = nullptr;
+        rc = mpb_plan_create(c, n, m, dtype, flags, &p);
+        if (rc == MPB_OK && margin) rc = mpb_plan_set_chain_margin(p, margin);
+        if (rc == MPB_OK) rc = mpb_plan_upload_series(p, T);
+        if (rc == MPB_OK) rc = mpb_plan_precompute(p);
+        if (rc == MPB_OK) rc = mpb_plan_compute(p);
+        if (rc == MPB_OK) rc = mpb_plan_finalize(p);
+        if (rc == MPB_OK) rc = mpb_plan_download(p, MP, MPI, nullptr);
+        if (rc == MPB_OK && timings) rc = mpb_plan_timings(p, timings);
+        if (rc == MPB_E_MARGIN) margin = std::max(8, p->margin_log2 - 2);
+        mpb_plan_destroy(p);
+        if (rc != MPB_E_MARGIN) break;
+    }
     return rc;
 }
 

@@ -670,7 +670,8 @@ template <typename T>
 __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ qt0,
               const double *__restrict__ Tser, const double *__restrict__ mu, int *__restrict__ hint,
-              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int seg_rows, int direct_band) {
+              const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int seg_rows, int direct_band,
+              int seg_first, int seg_stride) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
@@ -683,7 +684,7 @@ sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>
     int lo = 0, hi = nlb;
     const int item = blockIdx.x + item_begin;
     if (direct_band < 0) while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (item_start[mid] <= item) lo = mid; else hi = mid; }
-    const int seg = direct_band >= 0 ? (int)blockIdx.x : item - item_start[lo];
+    const int seg = direct_band >= 0 ? seg_first + (int)blockIdx.x * seg_stride : item - item_start[lo];   // direct: this rank's share of the band's segments
     const int band = direct_band >= 0 ? direct_band : item_start[nlb + 1 + lo];
     const int d0w = excl + band * BAND_W + warp * WARP_DIAGS;
     const int nrows = sublen - d0w;
@@ -785,7 +786,7 @@ __global__ void apply_hint_kernel(const int *__restrict__ hint, ProfileEntry *__
 }
 
 template <typename T>
-static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
+static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s) {
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
     const size_t smem = (size_t)cta_smem_bytes<T>();
@@ -795,23 +796,32 @@ static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, in
     if (e != cudaSuccess) return e;
     long long grid = p.items;
     int seg_rows = p.seg_rows;
-    if (p.sketch_band >= 0 && p.sketch_seg_rows > 0) {
+    const bool direct = p.sketch_band >= 0 && p.sketch_seg_rows > 0;
+    const int first = direct ? p.sketch_share_rank : 0, stride = direct ? p.sketch_share_world : 1;
+    if (direct) {
         seg_rows = p.sketch_seg_rows;
-        grid = (p.sublen - (p.excl + p.sketch_band * BAND_W) + seg_rows - 1) / seg_rows;
+        const long long nseg = (p.sublen - (p.excl + p.sketch_band * BAND_W) + seg_rows - 1) / seg_rows;
+        grid = nseg > first ? (nseg - first + stride - 1) / stride : 0;
     }
-    sketch_kernel<T><<<(unsigned)grid, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), qt0, p.series, p.mu, hint,
-                                                            p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, seg_rows,
-                                                            p.sketch_band >= 0 && p.sketch_seg_rows > 0 ? p.sketch_band : -1);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    apply_hint_kernel<<<(p.sublen + 255) / 256, 256, 0, s>>>(hint, prof, p.sublen);
+    if (grid > 0) {
+        sketch_kernel<T><<<(unsigned)grid, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), qt0, p.series, p.mu, hint,
+                                                                p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, seg_rows,
+                                                                direct ? p.sketch_band : -1, first, stride);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (!apply) return cudaSuccess;
+    return launch_apply_hint(hint, prof, p.sublen, s);
+}
+cudaError_t launch_apply_hint(const int *hint, ProfileEntry *prof, int sublen, cudaStream_t s) {
+    apply_hint_kernel<<<(sublen + 255) / 256, 256, 0, s>>>(hint, prof, sublen);
     return cudaGetLastError();
 }
-cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
-    return launch_sketch_t<double>(df_dg, nm, qt0, hint, prof, p, s);
+cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s) {
+    return launch_sketch_t<double>(df_dg, nm, qt0, hint, prof, p, apply, s);
 }
-cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
-    return launch_sketch_t<float>(df_dg, nm, qt0, hint, prof, p, s);
+cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s) {
+    return launch_sketch_t<float>(df_dg, nm, qt0, hint, prof, p, apply, s);
 }
 
 int band_count(int sublen, int excl) {

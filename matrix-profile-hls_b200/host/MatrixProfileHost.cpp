@@ -165,40 +165,23 @@ int RunMatrixProfileKernel(const Options &opt) {
     MPB_CHECK(mpb_device_count(&ndev));
     const int G = opt.gpus;
     if (G < 1 || G > ndev) { Log(Level::Error, "requested " + std::to_string(G) + " GPU(s), " + std::to_string(ndev) + " available"); return EXIT_FAILURE; }
-    std::vector<mpb_context *> ctx((size_t)G, nullptr);
-    std::vector<mpb_plan *> plan((size_t)G, nullptr);
-    auto cleanup = [&]() {
-        for (auto *p : plan) mpb_plan_destroy(p);
-        for (auto *c : ctx) mpb_context_destroy(c);
-    };
     const unsigned flags = opt.strict ? MPB_FLAG_STRICT : 0u;
     const int dtype = opt.use_float ? MPB_F32 : MPB_F64;
-    for (int g = 0; g < G; ++g) {
-        if (mpb_context_create(g, &ctx[g]) != MPB_OK || mpb_plan_create(ctx[g], n, m, dtype, flags, &plan[g]) != MPB_OK ||
-            mpb_plan_set_shard(plan[g], g, G) != MPB_OK) {
-            Log(Level::Error, std::string("device setup failed: ") + mpb_last_error());
-            cleanup();
-            return EXIT_FAILURE;
-        }
-    }
-
-    Log(Level::Verbose, "Copying memory to device...");                                                                // :89-92
-    Timer wall;
-    int rc = MPB_OK;
-    for (int g = 0; g < G && rc == MPB_OK; ++g) rc = mpb_plan_upload_series(plan[g], T.data());
-    Log(Level::Info, "Pre-Computing Statistics on Device");                                                           // was: on Host (:65-66)
-    for (int g = 0; g < G && rc == MPB_OK; ++g) rc = mpb_plan_precompute(plan[g]);
-    Log(Level::Verbose, "Starting Kernel Execution(s)...");
-    for (int g = 0; g < G && rc == MPB_OK; ++g) rc = mpb_plan_compute(plan[g]);                                        // chunk loop :101-137
-    if (rc == MPB_OK && G > 1) rc = mpb_plan_merge_peers(plan[0], plan.data() + 1, G - 1);                             // UpdateAggregates over NVLink
-    Log(Level::Info, "Performing Post-Computation on Device");
-    if (rc == MPB_OK) rc = mpb_plan_finalize(plan[0]);                                                                 // PostComputeAggregates :142
     std::vector<double> MP((size_t)(sublen > 0 ? sublen : 0));
     std::vector<int32_t> MPI(MP.size());
-    if (rc == MPB_OK) rc = mpb_plan_download(plan[0], MP.data(), MPI.data(), nullptr);
+    std::vector<mpb_timings> tms((size_t)G);
+
+    // The reference copies the input to every compute unit, enqueues the chunks round-robin, and merges on the host
+    // (:78-137).  Here: one host thread per GPU (mpb_compute_multi), each uploads the series, pre-computes, walks its
+    // diagonal bands, and the profiles are max-merged over NVLink with NCCL; rank 0 converts and downloads.
+    Log(Level::Verbose, "Copying memory to device...");                                                                // :89-92
+    Log(Level::Info, "Pre-Computing Statistics on Device");                                                           // was: on Host (:65-66)
+    Log(Level::Verbose, "Starting Kernel Execution(s)...");
+    Timer wall;
+    const int rc = mpb_compute_multi(G, nullptr, T.data(), n, m, dtype, flags, MP.data(), MPI.data(), tms.data());    // chunk loop :101-137 + :142
+    Log(Level::Info, "Performing Post-Computation on Device");
     if (rc != MPB_OK) {
         Log(Level::Error, std::string("matrix profile computation failed: ") + mpb_last_error());
-        cleanup();
         return EXIT_FAILURE;
     }
     const double wall_ms = wall.ElapsedMs();
@@ -206,9 +189,8 @@ int RunMatrixProfileKernel(const Options &opt) {
 
     double pre = 0, comp = 0, fin = 0, h2d = 0, d2h = 0;
     long long items = 0;
-    mpb_timings tm{};
     for (int g = 0; g < G; ++g) {
-        if (mpb_plan_timings(plan[g], &tm) != MPB_OK) continue;
+        const mpb_timings &tm = tms[(size_t)g];
         if (tm.precompute_ms > pre) pre = tm.precompute_ms;
         if (tm.compute_ms > comp) comp = tm.compute_ms;
         if (tm.h2d_ms > h2d) h2d = tm.h2d_ms;
@@ -219,7 +201,7 @@ int RunMatrixProfileKernel(const Options &opt) {
     profile.Push("0. Host <-> Device Copies", "series H2D (" + std::to_string(G) + " GPU)", h2d);
     profile.Push("0. Host <-> Device Copies", "profile + index D2H", d2h);
     profile.Push("1. Device-Side [Pre-Computation]", "mean / df / dg / inv / QT seeds", pre);                        // HostSideComputation.hpp:44
-    profile.Push("2. GPU Computation [" + kname + "]", "MatrixProfileKernelTLF [" + std::to_string(items) + " tiles on " + std::to_string(G) + " GPU]", comp);   // :121-122
+    profile.Push("2. GPU Computation [" + kname + "]", "MatrixProfileKernelTLF [" + std::to_string(items) + " tiles on " + std::to_string(G) + " GPU, NCCL merge included]", comp);   // :121-122
     profile.Push("3/4. Device-Side [Update-Aggregates + Post-Computation]", "merge + Pearson -> distance", fin);      // HostSideComputation.hpp:68,89
     if (g_verbose) {
         const double cells = (double)mpb_useful_cells(n, m);
@@ -229,11 +211,10 @@ int RunMatrixProfileKernel(const Options &opt) {
 
     if (opt.output) {
         Log(Level::Verbose, "Saving results (MP/MPI) to file...");
-        if (!WriteBinaryFile(*opt.output + ".mpb", MP) || !WriteBinaryFile(*opt.output + ".mpib", MPI)) { cleanup(); return EXIT_FAILURE; }   // :147-152
+        if (!WriteBinaryFile(*opt.output + ".mpb", MP) || !WriteBinaryFile(*opt.output + ".mpib", MPI)) return EXIT_FAILURE;   // :147-152
     }
     profile.Report();
     Log(Level::Verbose, "Terminating Host.");
-    cleanup();
     return EXIT_SUCCESS;
 }
 

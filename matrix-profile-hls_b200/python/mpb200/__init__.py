@@ -46,7 +46,8 @@ class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("precompute_ms", C.c_double), ("compute_ms", C.c_double), ("finalize_ms", C.c_double),
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("cells", C.c_int64), ("slow_updates", C.c_int64),
                 ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64), ("replays", C.c_int64),
-                ("chain_candidates", C.c_int64), ("chain_max_correction", C.c_double), ("chain_bound", C.c_double), ("chain_margin", C.c_double)]
+                ("chain_candidates", C.c_int64), ("chain_max_correction", C.c_double), ("chain_bound", C.c_double), ("chain_margin", C.c_double),
+                ("cells_walked", C.c_int64), ("reseeded_diagonals", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -59,7 +60,9 @@ EXPORTS = [
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_merge_select", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
-    "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_timings", "mpb_plan_mu_walked", "mpb_useful_cells", "mpb_measure_fma_peak",
+    "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_check", "mpb_plan_timings", "mpb_plan_mu_walked", "mpb_comm_unique_id", "mpb_comm_create", "mpb_comm_destroy",
+    "mpb_comm_rank", "mpb_comm_world", "mpb_plan_allreduce", "mpb_plan_compute_merged", "mpb_merge_point", "mpb_plan_total_bands",
+    "mpb_plan_sketch_share", "mpb_plan_hint_device_ptr", "mpb_plan_hint_count", "mpb_plan_apply_hint", "mpb_compute_multi", "mpb_useful_cells", "mpb_measure_fma_peak",
 ]
 
 
@@ -72,7 +75,8 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.mpb_last_error.restype = C.c_char_p
         L.mpb_version.restype = C.c_char_p
-        for f in ("mpb_context_stream", "mpb_buffer_device_ptr", "mpb_plan_series_device_ptr", "mpb_plan_mp_device_ptr", "mpb_plan_mpi_device_ptr"):
+        for f in ("mpb_context_stream", "mpb_buffer_device_ptr", "mpb_plan_series_device_ptr", "mpb_plan_mp_device_ptr", "mpb_plan_mpi_device_ptr",
+                  "mpb_plan_hint_device_ptr"):
             getattr(L, f).restype = C.c_void_p
             getattr(L, f).argtypes = [C.c_void_p]
         L.mpb_buffer_size.restype = C.c_size_t
@@ -288,6 +292,34 @@ class Plan:
     def set_log_entries(self, entries):
         _chk(lib().mpb_plan_set_log_entries(self._h, C.c_int64(entries)))
 
+    def sketch_share(self, band, share_rank, share_world):
+        """This rank's share (row segments share_rank, share_rank + share_world, ...) of the sketch of global band `band` into hint[]."""
+        _chk(lib().mpb_plan_sketch_share(self._h, C.c_int(band), C.c_int(share_rank), C.c_int(share_world)))
+
+    @property
+    def hint_ptr(self):
+        return lib().mpb_plan_hint_device_ptr(self._h)
+
+    @property
+    def hint_count(self):
+        return int(lib().mpb_plan_hint_count(self._h))
+
+    def apply_hint(self):
+        _chk(lib().mpb_plan_apply_hint(self._h))
+
+    def total_bands(self):
+        c = C.c_int(0)
+        _chk(lib().mpb_plan_total_bands(self._h, C.byref(c)))
+        return c.value
+
+    def allreduce(self, comm):
+        """Exact (corr, index) max of the ranks' profiles over NCCL, in place (result, or thresholds after merge_select(True))."""
+        _chk(lib().mpb_plan_allreduce(self._h, comm._h))
+
+    def compute_merged(self, comm):
+        """One rank's compute step of a multi-GPU job: shared sketch, first bands, threshold merge, rest, result merge."""
+        _chk(lib().mpb_plan_compute_merged(self._h, comm._h))
+
     def merge_peers(self, others):
         arr = (C.c_void_p * len(others))(*[o._h for o in others])
         _chk(lib().mpb_plan_merge_peers(self._h, arr, C.c_int(len(others))))
@@ -310,6 +342,10 @@ class Plan:
         _chk(lib().mpb_plan_download_input(self._h, _vp(out)))
         return out
 
+    def check(self):
+        """Waits for the plan's work; raises if the near-tie log overflowed or the corrections exceed the margin's reach."""
+        _chk(lib().mpb_plan_check(self._h))
+
     def mu_walked(self):
         w = C.c_int(0)
         _chk(lib().mpb_plan_mu_walked(self._h, C.byref(w)))
@@ -330,6 +366,54 @@ class Plan:
             self.close()
         except Exception:
             pass
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id():
+    """ncclGetUniqueId: 128 bytes to be handed to every rank of the job (e.g. torch.distributed.broadcast)."""
+    buf = (C.c_ubyte * COMM_ID_BYTES)()
+    _chk(lib().mpb_comm_unique_id(buf, C.c_size_t(COMM_ID_BYTES)))
+    return bytes(buf)
+
+
+def merge_point(total_bands, world):
+    return int(lib().mpb_merge_point(C.c_int(total_bands), C.c_int(world)))
+
+
+class Comm:
+    """One rank of a multi-GPU job: an NCCL communicator on the context's device (C ABI mpb_comm_*)."""
+
+    def __init__(self, ctx, unique_id, rank, world):
+        assert len(unique_id) == COMM_ID_BYTES
+        self.ctx, self.rank, self.world = ctx, rank, world
+        self._h = C.c_void_p()
+        _chk(lib().mpb_comm_create(ctx._h, C.c_char_p(bytes(unique_id)), C.c_int(rank), C.c_int(world), C.byref(self._h)))
+        ctx._children.add(self)
+
+    def close(self):
+        if self._h:
+            lib().mpb_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def matrix_profile_multi(T, m, ngpus, dtype=F64, flags=0, devices=None, return_timings=False):
+    """mpb_compute_multi: HOST buffers, ngpus GPUs of this process (one host thread each), NCCL merge."""
+    T = np.ascontiguousarray(T, dtype=np.float64)
+    sublen = T.size - m + 1
+    MP = np.empty(max(sublen, 0), np.float64)
+    MPI = np.empty(max(sublen, 0), np.int32)
+    tms = (Timings * ngpus)()
+    dev = (C.c_int * ngpus)(*devices) if devices is not None else None
+    _chk(lib().mpb_compute_multi(C.c_int(ngpus), dev, _vp(T), C.c_int(T.size), C.c_int(m), C.c_int(dtype), C.c_uint(flags), _vp(MP), _vp(MPI), tms))
+    return (MP, MPI, [t.as_dict() for t in tms]) if return_timings else (MP, MPI)
 
 
 def matrix_profile(T, m, dtype=F64, flags=0, ctx=None, return_timings=False):

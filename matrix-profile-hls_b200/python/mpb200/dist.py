@@ -1,18 +1,22 @@
-"""Multi-GPU plumbing: one process per GPU, diagonal bands dealt round-robin over the ranks
-(the reference's chunk -> compute-unit round-robin, host/MatrixProfileHost.cpp:101-128), and ONE exchange
-step: an element-wise max of the per-rank profiles (the reference's UpdateAggregates,
-include/host/HostSideComputation.hpp:72-90, which its host does serially).
+"""Multi-GPU plumbing for one-process-per-GPU jobs (torchrun): the compute step, the NCCL max-reduction and the merge
+schedule live in libmpb200.so (csrc/multi_gpu.cu, C ABI mpb_comm_* / mpb_plan_compute_merged); torch.distributed is only
+used to hand rank 0's NCCL unique id to the other ranks.
 
-A (float64 corr, int32 index) pair does not fit one 64-bit word exactly, so the max-reduction runs as
-two NCCL all-reduces over NVLink: MAX over the correlations viewed as int64 (corr >= +0.0, so the IEEE
-bit pattern is order-preserving), then MIN over the indices with every rank that does not hold the
-maximum contributing INT32_MAX.  The result is exact and independent of rank count and arrival order
-(ties -> smallest index, the same rule the band kernel's 128-bit CAS applies).
+Diagonal bands are dealt round-robin over the ranks (the reference's chunk -> compute-unit round-robin,
+host/MatrixProfileHost.cpp:101-128) and there is ONE exchange step: an element-wise max of the per-rank profiles (the
+reference's UpdateAggregates, include/host/HostSideComputation.hpp:72-90, which its host does serially).  A (float64 corr,
+int32 index) pair does not fit one 64-bit word exactly, so the reduction runs as two all-reduces: MAX over the correlations
+viewed as int64 (corr >= +0.0, so the IEEE bit pattern is order-preserving), then MIN over the indices with every rank that
+does not hold the maximum contributing INT32_MAX.  allreduce_profile / mask_index_torch restate that rule on torch tensors
+for the CPU (gloo) tests of the host logic.
 """
 import torch
 import torch.distributed as dist
 
+from . import COMM_ID_BYTES, Comm, comm_unique_id, merge_point
+
 INT32_MAX = 2**31 - 1
+WARM_BANDS_TOTAL = 48     # mirrors MPB_WARM_BANDS_TOTAL (csrc/multi_gpu.cu)
 
 
 def mask_index_torch(corr, index, corr_max):
@@ -35,44 +39,21 @@ def band_owner(band, world):
     return band % world
 
 
-def merge_plan_across_ranks(plan, corr_buf, index_buf, group=None):
-    """GPU path: export the plan's packed profile, all-reduce it over NCCL, import the merged profile.
-    corr_buf / index_buf are CUDA tensors (float64 / int32, sublen) owned by the caller and reused."""
-    plan.export(corr_buf.data_ptr(), index_buf.data_ptr())
-
-    def mask(mine, index, corr_max):
-        plan.mask_index(corr_max.data_ptr(), index.data_ptr())   # kernel: index <- mine==max ? index : INT32_MAX
-        return index
-
-    allreduce_profile(corr_buf, index_buf, mask_fn=mask, group=group)
-    plan.import_(corr_buf.data_ptr(), index_buf.data_ptr())
+def merge_points(total_bands, world):
+    """Local-band indices after which the ranks max-merge their thresholds before the final merge (mpb_merge_point): once,
+    when about WARM_BANDS_TOTAL bands have been walked in total.  A function of the JOB's band count, so that every rank takes
+    the same decision even when the bands do not divide evenly over the ranks."""
+    pt = merge_point(total_bands, world)
+    return [pt] if pt > 0 else []
 
 
-WARM_BANDS_TOTAL = 48     # diagonal bands (512 diagonals each) after which the filter thresholds are tight (see DESIGN.md section 5)
-
-
-def merge_points(nlb, world):
-    """Local-band indices after which the ranks max-merge their profiles before the final merge: once, when about
-    WARM_BANDS_TOTAL bands have been walked in total."""
-    warm = max(1, -(-WARM_BANDS_TOTAL // world))
-    return [warm] if world > 1 and warm < nlb else []
-
-
-def compute_merged(plan, corr_buf, index_buf, world, group=None):
-    """The multi-GPU compute step: every rank walks its first few bands, the profiles are max-merged (each rank's
-    filter thresholds then come from about WARM_BANDS_TOTAL bands of ALL ranks instead of its own few), then every
-    rank walks the rest of its bands and the profiles are merged again.  Returns the number of kernels launched
-    besides the tile kernel."""
-    nlb = plan.local_bands()
-    extra = 0
-    lo = 0
-    for pt in merge_points(nlb, world):
-        plan.compute_bands(lo, pt)
-        merge_plan_across_ranks(plan, corr_buf, index_buf, group=group)
-        extra += 3
-        lo = pt
-    plan.compute_bands(lo, -1)
-    if world > 1:
-        merge_plan_across_ranks(plan, corr_buf, index_buf, group=group)
-        extra += 3
-    return extra
+def make_comm(ctx, group=None):
+    """An mpb200.Comm for this rank of the default (or given) process group: rank 0 draws the NCCL unique id, the group's
+    broadcast hands it out (CPU tensor on gloo, CUDA tensor on nccl), every rank then joins ncclCommInitRank."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = torch.device("cuda", ctx.device) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    buf = torch.zeros(COMM_ID_BYTES, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        buf.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(buf, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return Comm(ctx, bytes(buf.cpu().numpy().tobytes()), rank, world)
