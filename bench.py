@@ -212,6 +212,7 @@ def run_gpu_arm(args):
     if world > 1:
         from mpb200.dist import make_comm
         comm = make_comm(ctx)               # communicator creation stays outside the timed region
+        plan.connect_peers(comm)            # every rank maps the others' threshold arrays (CUDA IPC over NVLink), once
         ctx.finish()
 
     def step(e2e, T_pinned):

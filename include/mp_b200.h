@@ -161,10 +161,11 @@ int mpb_plan_export(mpb_plan *plan, void *corr_out_dev, void *index_out_dev);
  * so that a min-reduction of index_dev picks the smallest index among the ranks holding the maximum. */
 int mpb_plan_mask_index(mpb_plan *plan, const void *corr_max_dev, void *index_dev);
 int mpb_plan_import(mpb_plan *plan, const void *corr_dev, const void *index_dev);
-/* Chain-carry mode keeps two profiles: the running bests that drive the filter (thresholds) and the result built from
- * the resolved candidates.  export / mask_index / import / merge_peers address the result (thresholds == 0, default)
- * or the thresholds (thresholds != 0: the early merge of a multi-GPU step). No effect in the other modes. */
-int mpb_plan_merge_select(mpb_plan *plan, int thresholds);
+/* Threshold sharing inside one process: every improvement this plan's tile kernel makes to its profile is also pushed to the
+ * threshold arrays of `others` (same problem; this device or peer-accessible ones), so a slot's threshold is discovered once per
+ * job.  One direction: call it on every plan of the job.  Thresholds are hints -- results do not depend on them. */
+int mpb_plan_share_thresholds(mpb_plan *plan, mpb_plan *const *others, int count);
+int mpb_plan_shared_with(mpb_plan *plan);           /* number of other plans / ranks this plan pushes to */
 /* Near-tie margin of the chain-carry mode: 2^-log2_inverse relative (8..21, default 18).  Candidates within the margin of a
  * slot's best are deferred to the resolve step; the margin must exceed the corrections (mpb_timings.chain_max_correction). */
 int mpb_plan_set_chain_margin(mpb_plan *plan, int log2_inverse);
@@ -200,13 +201,17 @@ int mpb_comm_create(mpb_context *ctx, const void *id, int rank, int world, mpb_c
 int mpb_comm_destroy(mpb_comm *comm);
 int mpb_comm_rank(mpb_comm *comm);
 int mpb_comm_world(mpb_comm *comm);
-/* Exact (corr, index) max of the ranks' profiles, in place, stream-ordered: ncclAllReduce MAX on the correlations' int64 bit
- * patterns, then MIN on the indices of the ranks that hold the maximum (ties -> smallest index).  Addresses the result
- * profile, or the filter thresholds after mpb_plan_merge_select(plan, 1). */
+/* Threshold sharing across the ranks (collective, one node): every rank maps the others' threshold arrays -- peer pointers inside
+ * one process, CUDA-IPC handles across processes, exchanged with one ncclAllGather -- and its tile kernel pushes every profile
+ * improvement to all of them over NVLink (red.max.u64 into peer memory) while it computes. */
+int mpb_plan_connect_peers(mpb_plan *plan, mpb_comm *comm);
+/* Exact (corr, index) max of the ranks' result profiles, in place, stream-ordered: ncclAllReduce MAX on the correlations' int64
+ * bit patterns, then MIN on the indices of the ranks that hold the maximum (ties -> smallest index). */
 int mpb_plan_allreduce(mpb_plan *plan, mpb_comm *comm);
 /* One rank's compute step of a multi-GPU job (after mpb_plan_set_shard(rank, world) and mpb_plan_precompute): shared sketch
- * of band 0 (each rank walks 1/world of its rows; one max-reduction), the first bands, max-merge of the thresholds, the
- * remaining bands, max-merge of the result.  Every rank then holds the job's profile; call mpb_plan_finalize on any. */
+ * of band 0 (each rank walks 1/world of its rows; one max-reduction), this rank's bands (thresholds flowing between the ranks
+ * all along when they are connected; else one max-merge after the first bands), max-merge of the result.  Every rank then
+ * holds the job's profile; call mpb_plan_finalize on any. */
 int mpb_plan_compute_merged(mpb_plan *plan, mpb_comm *comm);
 int mpb_merge_point(int total_bands, int world);   /* local bands walked before the threshold merge (0 = no early merge) */
 int mpb_plan_total_bands(mpb_plan *plan, int *count);   /* diagonal bands of the whole problem (all ranks) */

@@ -36,20 +36,25 @@ __global__ void mask_index_kernel(const ProfileEntry *__restrict__ prof, int sub
     index[i] = (e.corr == corr_max[i] && e.index >= 0) ? e.index : INT_MAX;
 }
 
-__global__ void import_kernel(ProfileEntry *__restrict__ prof, int sublen, const double *__restrict__ corr, const int32_t *__restrict__ index) {
+__global__ void import_kernel(ProfileEntry *__restrict__ prof, int sublen, const double *__restrict__ corr, const int32_t *__restrict__ index,
+                              unsigned long long *__restrict__ thr) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= sublen) return;
     ProfileEntry e; e.corr = corr[i]; e.index = index[i] == INT_MAX ? -1 : index[i]; e.pad = 0;
     prof[i] = e;
+    if (thr && e.corr > 0.0) atomicMax(thr + i, (unsigned long long)__double_as_longlong(e.corr));   // what the job knows is a threshold for this rank too
 }
 
 // Exact (corr, index) max of a peer GPU's profile into ours; `peer` is a P2P-mapped pointer, so the
 // loads cross NVLink directly (no staging copy).
-__global__ void merge_peer_kernel(ProfileEntry *__restrict__ prof, const ProfileEntry *__restrict__ peer, int sublen) {
+__global__ void merge_peer_kernel(ProfileEntry *__restrict__ prof, const ProfileEntry *__restrict__ peer, int sublen, unsigned long long *__restrict__ thr) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= sublen) return;
     const ProfileEntry a = prof[i], b = peer[i];
-    if (b.corr > a.corr || (b.corr == a.corr && (unsigned)b.index < (unsigned)a.index)) prof[i] = b;
+    if (b.corr > a.corr || (b.corr == a.corr && (unsigned)b.index < (unsigned)a.index)) {
+        prof[i] = b;
+        if (thr && b.corr > 0.0) atomicMax(thr + i, (unsigned long long)__double_as_longlong(b.corr));
+    }
 }
 
 #define GRID(n) ((n) + 255) / 256, 256
@@ -65,12 +70,12 @@ cudaError_t launch_mask_index(const ProfileEntry *prof, int sublen, const double
     mask_index_kernel<<<GRID(sublen), 0, s>>>(prof, sublen, corr_max, index);
     return cudaGetLastError();
 }
-cudaError_t launch_import(ProfileEntry *prof, int sublen, const double *corr, const int32_t *index, cudaStream_t s) {
-    import_kernel<<<GRID(sublen), 0, s>>>(prof, sublen, corr, index);
+cudaError_t launch_import(ProfileEntry *prof, int sublen, const double *corr, const int32_t *index, unsigned long long *thr, cudaStream_t s) {
+    import_kernel<<<GRID(sublen), 0, s>>>(prof, sublen, corr, index, thr);
     return cudaGetLastError();
 }
-cudaError_t launch_merge_peer(ProfileEntry *prof, const ProfileEntry *peer, int sublen, cudaStream_t s) {
-    merge_peer_kernel<<<GRID(sublen), 0, s>>>(prof, peer, sublen);
+cudaError_t launch_merge_peer(ProfileEntry *prof, const ProfileEntry *peer, int sublen, unsigned long long *thr, cudaStream_t s) {
+    merge_peer_kernel<<<GRID(sublen), 0, s>>>(prof, peer, sublen, thr);
     return cudaGetLastError();
 }
 

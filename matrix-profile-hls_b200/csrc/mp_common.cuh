@@ -91,6 +91,19 @@ struct ChainFix {
 __host__ __device__ inline double chain_lower(double v, double mu) { return v - mu * (v > MPB_CHAIN_FLOOR ? v : MPB_CHAIN_FLOOR); }   // v minus the margin
 
 
+// Filter thresholds.  thr[i] = a lower bound of the best correlation of subsequence i known to the JOB, as the bit pattern of a
+// non-negative double (orders like an integer, so one 64-bit atomic max raises it): the seed diagonal and the sketch pass put
+// borrowed bounds there, and every improvement the tile kernel's drain applies to its rank's profile is pushed to the thr[]
+// array of EVERY rank of the job -- its own in HBM, the peers' over NVLink (P2P / CUDA-IPC mapped memory, fire-and-forget
+// red.max.u64) -- so a slot's threshold is discovered once per job, not once per GPU.  The tile kernel's staging reads only
+// its own copy.  Thresholds are hints: stale or lost ones cost time, never correctness.
+constexpr int MAX_PEERS = 8;
+struct ThrShare {
+    unsigned long long *thr[MAX_PEERS];   // [0] this rank's array (np entries), [1 .. n) the peers'
+    int n;
+    int pad;
+};
+
 // Exact (corr, index) max into a global profile slot: larger corr wins, equal corr -> smaller index
 // (deterministic whatever the arrival order / GPU count).  Returns the slot's corr after the update
 // (the band kernel derives its filter threshold from it).

@@ -20,10 +20,10 @@ cudaError_t launch_stats_f32(const double *T, const double *mu, int n, int m, fl
 cudaError_t launch_norm_f64(const double *inv, int sublen, int np, double *nm, double *mnc, cudaStream_t s);
 cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, float *mnc, cudaStream_t s);
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s);
-// seeds every profile slot with the cell at lag `lag` (the first diagonal outside the exclusion zone), computed directly;
-// borrow > 0: as a borrowed lower bound {P * borrow, index -1} instead of the cell itself (chain-carry mode)
-cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s);
-cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s);
+// seeds every THRESHOLD with the cell at lag `lag` (the first diagonal outside the exclusion zone), computed directly and lowered by
+// max(rel * P, mu * max(P, CHAIN_FLOOR)): a borrowed lower bound -- the tile kernel meets the cell itself on its way
+cudaError_t launch_seed_thresholds_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, unsigned long long *thr, double rel, double mu_abs, cudaStream_t s);
+cudaError_t launch_seed_thresholds_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, unsigned long long *thr, double rel, double mu_abs, cudaStream_t s);
 cudaError_t launch_pack_input_f64(const double *df_dg, const double *inv, const double *qt0, int sublen, void *out, cudaStream_t s);
 cudaError_t launch_pack_input_f32(const float *df_dg, const float *inv, const float *qt0, int sublen, void *out, cudaStream_t s);
 
@@ -41,6 +41,7 @@ struct TileLaunch {
     int sketch_band = -1, sketch_seg_rows = 0;   // sketch launches only: walk this one band in segments of sketch_seg_rows rows (own cut; -1 / 0 = the items of the table)
     int sketch_share_rank = 0, sketch_share_world = 1;   // one-band sketch shared by a multi-GPU job: this launch walks segments rank, rank + world, ...
     ChainFix chain = {};                // chain-carry mode (fp64, re-seeded segments): log != nullptr switches it on
+    ThrShare share = {};                // threshold arrays of the job: [0] this rank's (np entries), then the peers'; n >= 1
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);
@@ -55,18 +56,19 @@ cudaError_t launch_inv_block_max(const double *inv, int sublen, int seg_rows, do
 cudaError_t launch_chain_resolve(const TileLaunch &p, int lb_begin, int lb_end, const double *inv, const double *imax, const ProfileEntry *prof, ProfileEntry *fin,
                                  unsigned long long *stats, cudaStream_t s);
 
-// sketch pass over the items of `p` (first bands of a step): hint[np] <- high words of per-slot lower bounds, then borrowed entries into prof
+// sketch pass over the items of `p` (first bands of a step): hint[np] <- high words of per-slot lower bounds, then into the thresholds p.share.thr[0]
 // apply = false: leave hint[] for a max-reduction across the ranks that share the sketch, then launch_apply_hint
-cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s);
-cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s);
-cudaError_t launch_apply_hint(const int *hint, ProfileEntry *prof, int sublen, cudaStream_t s);
+cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, const TileLaunch &p, bool apply, cudaStream_t s);
+cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, const TileLaunch &p, bool apply, cudaStream_t s);
+cudaError_t launch_apply_hint(const int *hint, unsigned long long *thr, int sublen, cudaStream_t s);
 
 // kernel (3): merge.cu
 cudaError_t launch_finalize(const ProfileEntry *prof, int sublen, int m, double *MP, int32_t *MPI, double *corr, cudaStream_t s);
 cudaError_t launch_export(const ProfileEntry *prof, int sublen, double *corr, int32_t *index, cudaStream_t s);
 cudaError_t launch_mask_index(const ProfileEntry *prof, int sublen, const double *corr_max, int32_t *index, cudaStream_t s);
-cudaError_t launch_import(ProfileEntry *prof, int sublen, const double *corr, const int32_t *index, cudaStream_t s);
-cudaError_t launch_merge_peer(ProfileEntry *prof, const ProfileEntry *peer, int sublen, cudaStream_t s);
+// import / merge_peer also raise the thresholds thr[] to the merged correlations
+cudaError_t launch_import(ProfileEntry *prof, int sublen, const double *corr, const int32_t *index, unsigned long long *thr, cudaStream_t s);
+cudaError_t launch_merge_peer(ProfileEntry *prof, const ProfileEntry *peer, int sublen, unsigned long long *thr, cudaStream_t s);
 
 // chunk-compatible MatrixProfileKernelTLF: chunk_tlf.cu
 cudaError_t launch_chunk_tlf_f64(int n, int m, int w, int iteration, const void *input, void *output, void *scratch, size_t scratch_bytes, cudaStream_t s);

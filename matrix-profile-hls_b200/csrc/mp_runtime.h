@@ -43,7 +43,9 @@ struct mpb_plan {
     mpb::ProfileEntry *prof = nullptr;                        // np slots: running bests = the tile kernel's filter thresholds
     mpb::ProfileEntry *fin = nullptr;                         // np slots: the result profile of the chain-carry mode (else unused; the result is prof)
     bool seq_mean = false, chain_fix = false;                 // mu by the reference's running recurrence; telescoped chain carry (mp_common.cuh)
-    bool merge_thresholds = false;                            // export / import / merge_peers address prof even in the chain-carry mode
+    unsigned long long *thr = nullptr;                        // np filter thresholds (mp_common.cuh ThrShare): own allocation, so that peers can map it
+    mpb::ThrShare share = {};                                 // [0] = thr, then the connected peers' arrays
+    void *ipc_opened[mpb::MAX_PEERS] = {};                    // peers' arrays opened through CUDA IPC (closed with the plan)
     double *seg_seed = nullptr, *seg_end = nullptr;           // chain carry: S_k / E_k of the work items of one launch chunk, [chunk_items][BAND_W]
     long long chunk_items = 0;                                // capacity of those arrays in work items
     mpb::ChainLogEntry *chain_log = nullptr;                  // LOG_SHARDS sub-logs of log_shard_cap candidates

@@ -22,6 +22,7 @@
 #include <new>
 #include <string>
 #include <thread>
+#include <unistd.h>
 
 namespace {
 
@@ -31,6 +32,7 @@ struct NcclApi {
     decltype(&ncclCommInitRank) CommInitRank = nullptr;
     decltype(&ncclCommDestroy) CommDestroy = nullptr;
     decltype(&ncclAllReduce) AllReduce = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
     decltype(&ncclGetErrorString) GetErrorString = nullptr;
     decltype(&ncclGetVersion) GetVersion = nullptr;
     std::string error;
@@ -51,6 +53,7 @@ NcclApi &nccl() {
         MPB_SYM(CommInitRank, ncclCommInitRank);
         MPB_SYM(CommDestroy, ncclCommDestroy);
         MPB_SYM(AllReduce, ncclAllReduce);
+        MPB_SYM(AllGather, ncclAllGather);
         MPB_SYM(GetErrorString, ncclGetErrorString);
         MPB_SYM(GetVersion, ncclGetVersion);
 #undef MPB_SYM
@@ -118,8 +121,59 @@ int mpb_comm_destroy(mpb_comm *c) {
 int mpb_comm_rank(mpb_comm *c) { return c ? c->rank : -1; }
 int mpb_comm_world(mpb_comm *c) { return c ? c->world : 0; }
 
-// Exact (corr, index) max of the plans' profiles across the communicator, in place (the result profile, or the filter
-// thresholds after mpb_plan_merge_select(plan, 1)).  Stream-ordered on the context's stream; no host synchronisation.
+// Threshold sharing across the ranks of the communicator (mp_common.cuh ThrShare): every rank maps the threshold arrays of all
+// the others -- raw peer pointers inside one process, CUDA-IPC handles across processes, exchanged with one ncclAllGather --
+// and from then on pushes every profile improvement to all of them over NVLink.  Collective; one node.
+int mpb_plan_connect_peers(mpb_plan *p, mpb_comm *c) {
+    if (!p || !c) return fail(MPB_E_INVALID, "null argument");
+    if (p->ctx != c->ctx) return fail(MPB_E_INVALID, "plan and communicator belong to different contexts");
+    if (c->world > mpb::MAX_PEERS) return fail(MPB_E_INVALID, "threshold sharing supports up to %d ranks", mpb::MAX_PEERS);
+    if (c->world == 1) return MPB_OK;
+    struct Rec { long long pid; int device; int sublen; unsigned long long ptr; cudaIpcMemHandle_t handle; char pad[96 - 24 - sizeof(cudaIpcMemHandle_t)]; };
+    static_assert(sizeof(Rec) == 96, "record size");
+    cudaStream_t s = p->ctx->stream;
+    CU(cudaSetDevice(p->ctx->device));
+    std::vector<Rec> recs((size_t)c->world);
+    Rec &me = recs[(size_t)c->rank];
+    memset(&me, 0, sizeof me);
+    me.pid = (long long)getpid(); me.device = p->ctx->device; me.sublen = p->sublen; me.ptr = (unsigned long long)(uintptr_t)p->thr;
+    CU(cudaIpcGetMemHandle(&me.handle, p->thr));
+    Rec *dev = nullptr;
+    CU(cudaMalloc((void **)&dev, sizeof(Rec) * recs.size()));
+    cudaError_t e = cudaMemcpyAsync(dev + c->rank, &me, sizeof me, cudaMemcpyHostToDevice, s);
+    ncclResult_t nr = ncclSuccess;
+    if (e == cudaSuccess) nr = nccl().AllGather(dev + c->rank, dev, sizeof(Rec), ncclInt8, c->comm, s);
+    if (e == cudaSuccess && nr == ncclSuccess) e = cudaMemcpyAsync(recs.data(), dev, sizeof(Rec) * recs.size(), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess && nr == ncclSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(dev);
+    if (nr != ncclSuccess) return fail(MPB_E_CUDA, "ncclAllGather: %s", nccl().GetErrorString(nr));
+    CU(e);
+    for (void *&q : p->ipc_opened) if (q) { cudaIpcCloseMemHandle(q); q = nullptr; }
+    p->share.n = 1;
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) continue;
+        const Rec &o = recs[(size_t)r];
+        if (o.sublen != p->sublen) return fail(MPB_E_INVALID, "rank %d runs a different problem", r);
+        void *ptr = nullptr;
+        if (o.pid == me.pid) {                       // same process (host thread per GPU): the pointer is valid here once peer access is on
+            if (o.device != p->ctx->device) {
+                cudaError_t pe = cudaDeviceEnablePeerAccess(o.device, 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) return fail(MPB_E_CUDA, "cudaDeviceEnablePeerAccess(%d): %s", o.device, cudaGetErrorString(pe));
+                cudaGetLastError();
+            }
+            ptr = (void *)(uintptr_t)o.ptr;
+        } else {
+            cudaError_t ie = cudaIpcOpenMemHandle(&ptr, o.handle, cudaIpcMemLazyEnablePeerAccess);
+            if (ie != cudaSuccess) { cudaGetLastError(); return fail(MPB_E_CUDA, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(ie)); }
+            p->ipc_opened[p->share.n] = ptr;
+        }
+        p->share.thr[p->share.n++] = (unsigned long long *)ptr;
+    }
+    return MPB_OK;
+}
+
+// Exact (corr, index) max of the plans' result profiles across the communicator, in place (every rank's thresholds rise to the
+// merged correlations as well).  Stream-ordered on the context's stream; no host synchronisation.
 int mpb_plan_allreduce(mpb_plan *p, mpb_comm *c) {
     if (!p || !c) return fail(MPB_E_INVALID, "null argument");
     if (p->ctx != c->ctx) return fail(MPB_E_INVALID, "plan and communicator belong to different contexts");
@@ -175,12 +229,12 @@ int mpb_plan_compute_merged(mpb_plan *p, mpb_comm *c) {
         rc = mpb_plan_apply_hint(p);
         if (rc != MPB_OK) return rc;
     }
-    const int pt = mpb_merge_point(total, c->world);
+    // ranks that push their improvements to one another (mpb_plan_connect_peers) need no merge on the way; otherwise the
+    // results so far are max-merged once the first bands are walked, which also lifts every rank's thresholds
+    const int pt = p->share.n > 1 ? 0 : mpb_merge_point(total, c->world);
     if (pt > 0) {
         rc = mpb_plan_compute_bands(p, 0, pt);
-        if (rc == MPB_OK) rc = mpb_plan_merge_select(p, 1);
         if (rc == MPB_OK) rc = mpb_plan_allreduce(p, c);
-        if (rc == MPB_OK) rc = mpb_plan_merge_select(p, 0);
         if (rc == MPB_OK) rc = mpb_plan_compute_bands(p, pt, -1);
     } else {
         rc = mpb_plan_compute_bands(p, 0, -1);
@@ -248,7 +302,11 @@ int mpb_compute_multi(int ngpus, const int *devices, const double *T, int n, int
         step(r);
         if (rv.arrive() == MPB_OK) {                       // nobody enters the NCCL rendezvous unless everybody can
             step(mpb_comm_create(ctx, id, g, ngpus, &comm));
-            if (rv.arrive() == MPB_OK) {
+            if (rv.arrive() == MPB_OK && ngpus <= mpb::MAX_PEERS) {
+                step(mpb_plan_connect_peers(plan, comm));
+                rv.arrive();
+            }
+            if (rv.failed == MPB_OK) {
                 r = mpb_plan_upload_series(plan, T);
                 if (r == MPB_OK) r = mpb_plan_precompute(plan);
                 if (r == MPB_OK) r = mpb_plan_compute_merged(plan, comm);

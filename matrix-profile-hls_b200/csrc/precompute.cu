@@ -435,8 +435,8 @@ __global__ void norm_kernel(const OutT *__restrict__ inv, int sublen, int np, Ou
 // ---------------------------------------------------------------------------------------------
 template <typename OutT>
 __global__ void __launch_bounds__(STATS_THREADS)
-seed_profile_kernel(const double *__restrict__ T, const double *__restrict__ mu, const OutT *__restrict__ inv, int n, int m, int lag,
-                    ProfileEntry *prof, double borrow) {
+seed_thresholds_kernel(const double *__restrict__ T, const double *__restrict__ mu, const OutT *__restrict__ inv, int n, int m, int lag,
+                       unsigned long long *thr, double rel, double mu_abs) {
     extern __shared__ double sm[];                   // T[i0 .. i0 + STATS_THREADS + m + lag)
     const int sublen = n - m + 1;
     const int i0 = blockIdx.x * STATS_THREADS;
@@ -456,12 +456,11 @@ seed_profile_kernel(const double *__restrict__ T, const double *__restrict__ mu,
     const OutT qt = (OutT)(q0 + q1);
     const double p = (double)((qt * inv[i]) * inv[j]);
     if (p > 0.0) {
-        if (borrow > 0.0) {     // chain-carry mode (borrow = the near-tie margin): a lower bound, four margins below the cell; the
-            const double lb = chain_lower(p, 4.0 * borrow);                        // tile kernel meets the cell itself and replaces it
-            if (lb > 0.0) { profile_update(prof + i, lb, -1); profile_update(prof + j, lb, -1); }
-        } else {
-            profile_update(prof + i, p, j);
-            profile_update(prof + j, p, i);
+        const double lb = p - fmax(rel * p, mu_abs * fmax(p, MPB_CHAIN_FLOOR));
+        if (lb > 0.0) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(lb);
+            atomicMax(thr + i, bits);
+            atomicMax(thr + j, bits);
         }
     }
 }
@@ -560,22 +559,22 @@ cudaError_t launch_norm_f32(const float *inv, int sublen, int np, float *nm, flo
     return cudaGetLastError();
 }
 template <typename OutT>
-static cudaError_t launch_seed_t(const double *T, const double *mu, const OutT *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s) {
+static cudaError_t launch_seed_t(const double *T, const double *mu, const OutT *inv, int n, int m, int lag, unsigned long long *thr, double rel, double mu_abs, cudaStream_t s) {
     const int sublen = n - m + 1;
     if (sublen - lag <= 0) return cudaSuccess;
     const size_t smem = sizeof(double) * (size_t)(STATS_THREADS + m + lag);
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(seed_profile_kernel<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(seed_thresholds_kernel<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    seed_profile_kernel<OutT><<<(sublen - lag + STATS_THREADS - 1) / STATS_THREADS, STATS_THREADS, smem, s>>>(T, mu, inv, n, m, lag, prof, borrow);
+    seed_thresholds_kernel<OutT><<<(sublen - lag + STATS_THREADS - 1) / STATS_THREADS, STATS_THREADS, smem, s>>>(T, mu, inv, n, m, lag, thr, rel, mu_abs);
     return cudaGetLastError();
 }
-cudaError_t launch_seed_profile_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s) {
-    return launch_seed_t<double>(T, mu, inv, n, m, lag, prof, borrow, s);
+cudaError_t launch_seed_thresholds_f64(const double *T, const double *mu, const double *inv, int n, int m, int lag, unsigned long long *thr, double rel, double mu_abs, cudaStream_t s) {
+    return launch_seed_t<double>(T, mu, inv, n, m, lag, thr, rel, mu_abs, s);
 }
-cudaError_t launch_seed_profile_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, ProfileEntry *prof, double borrow, cudaStream_t s) {
-    return launch_seed_t<float>(T, mu, inv, n, m, lag, prof, borrow, s);
+cudaError_t launch_seed_thresholds_f32(const double *T, const double *mu, const float *inv, int n, int m, int lag, unsigned long long *thr, double rel, double mu_abs, cudaStream_t s) {
+    return launch_seed_t<float>(T, mu, inv, n, m, lag, thr, rel, mu_abs, s);
 }
 cudaError_t launch_profile_init(ProfileEntry *prof, int count, cudaStream_t s) {
     profile_init_kernel<<<(count + 255) / 256, 256, 0, s>>>(prof, count);

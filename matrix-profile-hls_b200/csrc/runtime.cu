@@ -236,7 +236,8 @@ int mpb_plan_destroy(mpb_plan *p) {
     if (!p || !reg_take(g_plans, p)) return MPB_OK;
     cudaSetDevice(p->ctx->device);
     cudaStreamSynchronize(p->ctx->stream);
-    void *ptrs[] = {p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start, p->hint,
+    for (void *q : p->ipc_opened) if (q) cudaIpcCloseMemHandle(q);
+    void *ptrs[] = {p->thr, p->T, p->mu, p->df_dg, p->inv, p->qt0, p->nm, p->mnc, p->prof, p->MP, p->corr, p->MPI, p->slow_counter, p->item_start, p->hint,
                     p->fin, p->seg_seed, p->seg_end, p->chain_log, p->log_count, p->chain_stats, p->inv_blockmax, p->mu_scratch};
     for (void *q : ptrs) if (q) cudaFree(q);
     for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
@@ -284,6 +285,8 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
     ALLOC(p->slow_counter, 4 * sizeof(unsigned long long));
     ALLOC(p->hint, sizeof(int) * np);
+    ALLOC(p->thr, sizeof(unsigned long long) * np);
+    p->share.thr[0] = p->thr; p->share.n = 1;
     if (p->seq_mean && !(flags & MPB_FLAG_MU_WALK)) ALLOC(p->mu_scratch, mpb::mu_scan_scratch_bytes(n, m));
     if (p->chain_fix) {
         ALLOC(p->fin, sizeof(mpb::ProfileEntry) * np);
@@ -412,6 +415,7 @@ int mpb_plan_precompute(mpb_plan *p) {
     if (p->dtype == MPB_F64) CU(mpb::launch_norm_f64((const double *)p->inv, p->sublen, p->np, (double *)p->nm, (double *)p->mnc, s));
     else CU(mpb::launch_norm_f32((const float *)p->inv, p->sublen, p->np, (float *)p->nm, (float *)p->mnc, s));
     CU(mpb::launch_profile_init(p->prof, p->np, s));
+    CU(cudaMemsetAsync(p->thr, 0, sizeof(unsigned long long) * (size_t)p->np, s));
     p->tm.launches = 4;
     if (p->chain_fix) {
         CU(mpb::launch_profile_init(p->fin, p->np, s));
@@ -420,10 +424,12 @@ int mpb_plan_precompute(mpb_plan *p) {
         p->tm.launches += 2;
     }
     if (!(p->flags & (MPB_FLAG_STRICT | MPB_FLAG_NO_SEED))) {
-        // chain-carry mode: the seed is a borrowed lower bound (4 margins below the cell, index -1), never a result
-        const double borrow = p->chain_fix ? std::ldexp(1.0, -p->margin_log2) : 0.0;
-        if (p->dtype == MPB_F64) CU(mpb::launch_seed_profile_f64(p->T, p->mu, (const double *)p->inv, p->n, p->m, p->excl, p->prof, borrow, s));
-        else CU(mpb::launch_seed_profile_f32(p->T, p->mu, (const float *)p->inv, p->n, p->m, p->excl, p->prof, 0.0, s));
+        // the seed is a borrowed lower bound in the thresholds, never a result: lowered by what separates its direct dot product from
+        // the chain's value of the same cell (rounding; in the chain-carry mode four near-tie margins)
+        const double rel = p->dtype == MPB_F64 ? std::ldexp(1.0, -20) : std::ldexp(1.0, -12);
+        const double mu_abs = p->chain_fix ? 4.0 * std::ldexp(1.0, -p->margin_log2) : 0.0;
+        if (p->dtype == MPB_F64) CU(mpb::launch_seed_thresholds_f64(p->T, p->mu, (const double *)p->inv, p->n, p->m, p->excl, p->thr, rel, mu_abs, s));
+        else CU(mpb::launch_seed_thresholds_f32(p->T, p->mu, (const float *)p->inv, p->n, p->m, p->excl, p->thr, rel, mu_abs, s));
         p->tm.launches += 1;
     }
     CU(cudaEventRecord(p->ev[3], s));
@@ -474,7 +480,8 @@ int mpb_plan_sketch_share(mpb_plan *p, int band, int share_rank, int share_world
     sl.seg_rows = p->seg_rows_eff; sl.strict = false; sl.series = p->T; sl.mu = p->mu; sl.item_start = p->item_start; sl.nlb = p->nlb;
     sl.item_begin = 0; sl.items = 1; sl.counters = nullptr;
     sl.sketch_band = band; sl.sketch_seg_rows = MPB_SKETCH_SEG_ROWS; sl.sketch_share_rank = share_rank; sl.sketch_share_world = share_world;
-    CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, false, s));
+    sl.share = p->share;
+    CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, sl, false, s));
     p->tm.launches += 1;
     p->sketched = true;
     return MPB_OK;
@@ -484,7 +491,7 @@ int mpb_plan_hint_count(mpb_plan *p) { return p ? p->np : 0; }
 int mpb_plan_apply_hint(mpb_plan *p) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
     CU(cudaSetDevice(p->ctx->device));
-    CU(mpb::launch_apply_hint(p->hint, p->prof, p->sublen, p->ctx->stream));
+    CU(mpb::launch_apply_hint(p->hint, p->thr, p->sublen, p->ctx->stream));
     p->tm.launches += 1;
     return MPB_OK;
 }
@@ -506,6 +513,7 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
     tl.item_begin = p->nlb > 0 ? p->table_host[lb_begin] : 0;
     tl.items = p->nlb > 0 ? (long long)p->table_host[lb_end] - tl.item_begin : 0;
     tl.counters = p->slow_counter;
+    tl.share = p->share;
     if (lb_begin == 0) {                      // first launch of a step: statistics and the compute timer start here
         rc = plan_step_begin(p);
         if (rc != MPB_OK) return rc;
@@ -526,8 +534,8 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
                 sl.sketch_band = p->table_host[(size_t)p->nlb + 1];
                 sl.sketch_seg_rows = MPB_SKETCH_SEG_ROWS;
             }
-            if (p->dtype == MPB_F64) CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, p->prof, sl, true, s));
-            else CU(mpb::launch_sketch_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->qt0, p->hint, p->prof, sl, true, s));
+            if (p->dtype == MPB_F64) CU(mpb::launch_sketch_f64((const double *)p->df_dg, (const double *)p->nm, (const double *)p->qt0, p->hint, sl, true, s));
+            else CU(mpb::launch_sketch_f32((const float *)p->df_dg, (const float *)p->nm, (const float *)p->qt0, p->hint, sl, true, s));
             p->tm.launches += sl.items > 0 ? 2 : 0;
             p->sketched = true;
         }
@@ -564,14 +572,32 @@ int mpb_plan_compute_bands(mpb_plan *p, int lb_begin, int lb_end) {
 
 int mpb_plan_compute(mpb_plan *p) { return mpb_plan_compute_bands(p, 0, -1); }
 
-// which profile export / mask_index / import / merge_peers address in the chain-carry mode
-static mpb::ProfileEntry *merge_profile(mpb_plan *p) { return p->chain_fix && !p->merge_thresholds ? p->fin : p->prof; }
+// the profile export / mask_index / import / merge_peers address: the result
+static mpb::ProfileEntry *merge_profile(mpb_plan *p) { return p->chain_fix ? p->fin : p->prof; }
 
-int mpb_plan_merge_select(mpb_plan *p, int thresholds) {
-    if (!p) return fail(MPB_E_INVALID, "plan is null");
-    p->merge_thresholds = thresholds != 0;
+// Threshold sharing inside one process: improvements this plan's tile kernel makes are also pushed to the threshold arrays of
+// `others` (plans of the same problem on this or on peer-accessible devices).  One direction: call it on every plan of the job.
+int mpb_plan_share_thresholds(mpb_plan *p, mpb_plan *const *others, int count) {
+    if (!p || (count > 0 && !others)) return fail(MPB_E_INVALID, "null argument");
+    if (count + 1 > mpb::MAX_PEERS) return fail(MPB_E_INVALID, "at most %d plans can share thresholds", mpb::MAX_PEERS);
+    CU(cudaSetDevice(p->ctx->device));
+    p->share.n = 1;
+    for (int k = 0; k < count; ++k) {
+        mpb_plan *o = others[k];
+        if (!o || o == p || o->sublen != p->sublen) return fail(MPB_E_INVALID, "peer plan %d does not match", k);
+        if (o->ctx->device != p->ctx->device) {
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, p->ctx->device, o->ctx->device));
+            if (!can) return fail(MPB_E_CUDA, "device %d cannot access device %d over P2P", p->ctx->device, o->ctx->device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->ctx->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(MPB_E_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+        p->share.thr[p->share.n++] = o->thr;
+    }
     return MPB_OK;
 }
+int mpb_plan_shared_with(mpb_plan *p) { return p ? p->share.n - 1 : 0; }
 
 int mpb_plan_set_chain_margin(mpb_plan *p, int log2_inverse) {
     if (!p) return fail(MPB_E_INVALID, "plan is null");
@@ -606,7 +632,7 @@ int mpb_plan_mask_index(mpb_plan *p, const void *corr_max, void *index) {
 int mpb_plan_import(mpb_plan *p, const void *corr, const void *index) {
     if (!p || !corr || !index) return fail(MPB_E_INVALID, "null argument");
     CU(cudaSetDevice(p->ctx->device));
-    CU(mpb::launch_import(merge_profile(p), p->sublen, (const double *)corr, (const int32_t *)index, p->ctx->stream));
+    CU(mpb::launch_import(merge_profile(p), p->sublen, (const double *)corr, (const int32_t *)index, p->thr, p->ctx->stream));
     p->tm.launches += 1;
     return MPB_OK;
 }
@@ -631,7 +657,7 @@ int mpb_plan_merge_peers(mpb_plan *p, mpb_plan *const *others, int count) {
         CU(cudaSetDevice(p->ctx->device));
         CU(cudaStreamWaitEvent(p->ctx->stream, o->ev[7], 0));
         if (p->chain_fix != o->chain_fix) return fail(MPB_E_INVALID, "peer plan %d runs in a different mode", k);
-        CU(mpb::launch_merge_peer(merge_profile(p), merge_profile(o), p->sublen, p->ctx->stream));
+        CU(mpb::launch_merge_peer(merge_profile(p), merge_profile(o), p->sublen, p->thr, p->ctx->stream));
         p->tm.launches += 1;
     }
     return MPB_OK;

@@ -92,7 +92,7 @@ struct WarpSmem {
     static constexpr int NK = (COL_STRIDE + 3) / 4 * 4;
     static constexpr int HITS_BYTES = HCAP * DPT * (int)sizeof(T) + HCAP * 8;
     static constexpr int BYTES = ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * (int)sizeof(T) + COL_SLOTS * 8 +
-                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16 + WCAP * 16 + (int)sizeof(WarpLog);
+                                 HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16 + WCAP * 16 + (int)sizeof(WarpLog) + (int)((sizeof(ThrShare) + 15) / 16 * 16);
     T2 *rowA;         // [i] = {df_r, dg_r}
     double2 *rowC;    // [i] = {best correlation of the row as this warp knows it, inv_r}
     T2 *colA;         // [slot(x)] = {df_c, dg_c}
@@ -107,6 +107,7 @@ struct WarpSmem {
     unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] blocks replayed
     Winner *wlist;    // cells that improved the warp's view of a slot, waiting for the profile update
     WarpLog *wlog;    // chain-carry mode: where this warp appends its candidates
+    ThrShare *wsh;    // the job's threshold arrays (own + peers): where improvements are pushed
     __device__ __forceinline__ explicit WarpSmem(unsigned char *base) {
         rowA = reinterpret_cast<T2 *>(base);
         rowC = reinterpret_cast<double2 *>(rowA + ROWS_STAGED);
@@ -122,6 +123,7 @@ struct WarpSmem {
         stat = reinterpret_cast<unsigned *>(wK + NK);
         wlist = reinterpret_cast<Winner *>(stat + 4);
         wlog = reinterpret_cast<WarpLog *>(wlist + WCAP);
+        wsh = reinterpret_cast<ThrShare *>(wlog + 1);
     }
 };
 static_assert(WarpSmem<double>::BYTES % 16 == 0 && WarpSmem<float>::BYTES % 16 == 0, "warp slices stay 16-byte aligned");
@@ -239,8 +241,13 @@ __device__ __forceinline__ unsigned apply_winners(WarpSmem<T> &S, int cnt, int r
         const int2 mt = S.hitM[h];
         const int row = r0 + mt.x, col = c0 + mt.y + j;
         const int slot = (w.code >> 16) ? row : col, idx = (w.code >> 16) ? col : row;
-        if (LOG) wins += profile_update_log(prof, slot, w.v, idx, S.wlog) == w.v;
-        else wins += profile_update(prof + slot, w.v, idx) == w.v;
+        const double after = LOG ? profile_update_log(prof, slot, w.v, idx, S.wlog) : profile_update(prof + slot, w.v, idx);
+        if (after == w.v) {                      // the rank's best for this slot: raise the job's thresholds (own copy and every peer's)
+            ++wins;
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(w.v);
+            const int np = S.wsh->n;
+            for (int k = 0; k < np; ++k) atomicMax(S.wsh->thr[k] + slot, bits);
+        }
     }
     __syncwarp();
     return wins;
@@ -454,7 +461,7 @@ __global__ void __launch_bounds__(BAND_THREADS, ctas_per_sm<T>())
 tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::T2 *__restrict__ nm, const T *__restrict__ mnc,
             const T *__restrict__ qt0, const double *__restrict__ Tser, const double *__restrict__ mu, ProfileEntry *prof,
             const int *__restrict__ item_start, int item_begin, int nlb, int n, int m, int sublen, int excl, int rank, int world, int seg_rows,
-            unsigned long long *counters, const ChainFix cf) {
+            unsigned long long *counters, const ChainFix cf, const ThrShare sh) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem<T> S(smem_raw + warp * WarpSmem<T>::BYTES);
@@ -481,6 +488,12 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 
     int hitcnt = 0;                 // warp-uniform: hits parked in the buffer
     if (lane < 4) S.stat[lane] = 0;
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < MAX_PEERS; ++k) S.wsh->thr[k] = sh.thr[k];
+        S.wsh->n = sh.n; S.wsh->pad = 0;
+    }
+    const double *__restrict__ thr = reinterpret_cast<const double *>(sh.thr[0]);
     if (LOG && lane == 0) {
         const unsigned shard = (blockIdx.x * BAND_WARPS + warp) % LOG_SHARDS;
         WarpLog wl; wl.log = cf.log + (size_t)shard * cf.shard_cap; wl.count = cf.log_count + shard * 16; wl.cap = cf.shard_cap;
@@ -515,7 +528,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             if (i < ROWS_STAGED) {
                 S.rowA[i] = df_dg[r0 + i];
                 const T2 nv = nm[r0 + i];                       // {norm, inv}; norm = +inf on the padding
-                double rbest = __ldcg(&prof[r0 + i].corr);
+                double rbest = __ldcg(thr + r0 + i);
                 if (LOG) rbest = lower_thr(rbest, km);
                 S.rowC[i] = make_double2(rbest, (double)nv.y);
                 const T best = max((T)rbest, tiny_best(T(0)));  // never 0: 0 * inf would be a NaN
@@ -546,7 +559,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
                 const int x = min(lane + 32 * k, COL_WIN - 1);
                 ca[k] = df_dg[c0 + x];
                 nv[k] = nm[c0 + x];                         // {norm_c, inv_c}
-                cb[k] = __ldcg(&prof[c0 + x].corr);
+                cb[k] = __ldcg(thr + c0 + x);
                 if (LOG) cb[k] = lower_thr(cb[k], km);
             }
 #pragma unroll
@@ -571,7 +584,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             const int p = col_slot(x);
             S.colA[p] = df_dg[c0 + x];
             const T2 nv = nm[c0 + x];                       // {norm_c, inv_c}
-            double cbest = __ldcg(&prof[c0 + x].corr);
+            double cbest = __ldcg(thr + c0 + x);
             if (LOG) cbest = lower_thr(cbest, km);
             S.colBest[p] = cbest;
             S.colInv[p] = nv.y;
@@ -776,17 +789,16 @@ sketch_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>
 }
 
 // hint[i] (high word of a lower bound of slot i's best correlation) -> borrowed profile entry {bound, -1}
-__global__ void apply_hint_kernel(const int *__restrict__ hint, ProfileEntry *__restrict__ prof, int sublen) {
+__global__ void apply_hint_kernel(const int *__restrict__ hint, unsigned long long *__restrict__ thr, int sublen) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= sublen) return;
     const int h = hint[i] - 2;                                  // two high-word ulps (2e-6 relative) below any rounding concern
     if (h <= 0) return;
-    const double v = __hiloint2double(h, 0);
-    if (v > prof[i].corr) { ProfileEntry e; e.corr = v; e.index = -1; e.pad = 0; prof[i] = e; }
+    atomicMax(thr + i, (unsigned long long)(unsigned)h << 32);
 }
 
 template <typename T>
-static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s) {
+static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, int *hint, const TileLaunch &p, bool apply, cudaStream_t s) {
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
     const size_t smem = (size_t)cta_smem_bytes<T>();
@@ -811,17 +823,17 @@ static cudaError_t launch_sketch_t(const T *df_dg, const T *nm, const T *qt0, in
         if (e != cudaSuccess) return e;
     }
     if (!apply) return cudaSuccess;
-    return launch_apply_hint(hint, prof, p.sublen, s);
+    return launch_apply_hint(hint, p.share.thr[0], p.sublen, s);
 }
-cudaError_t launch_apply_hint(const int *hint, ProfileEntry *prof, int sublen, cudaStream_t s) {
-    apply_hint_kernel<<<(sublen + 255) / 256, 256, 0, s>>>(hint, prof, sublen);
+cudaError_t launch_apply_hint(const int *hint, unsigned long long *thr, int sublen, cudaStream_t s) {
+    apply_hint_kernel<<<(sublen + 255) / 256, 256, 0, s>>>(hint, thr, sublen);
     return cudaGetLastError();
 }
-cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s) {
-    return launch_sketch_t<double>(df_dg, nm, qt0, hint, prof, p, apply, s);
+cudaError_t launch_sketch_f64(const double *df_dg, const double *nm, const double *qt0, int *hint, const TileLaunch &p, bool apply, cudaStream_t s) {
+    return launch_sketch_t<double>(df_dg, nm, qt0, hint, p, apply, s);
 }
-cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, ProfileEntry *prof, const TileLaunch &p, bool apply, cudaStream_t s) {
-    return launch_sketch_t<float>(df_dg, nm, qt0, hint, prof, p, apply, s);
+cudaError_t launch_sketch_f32(const float *df_dg, const float *nm, const float *qt0, int *hint, const TileLaunch &p, bool apply, cudaStream_t s) {
+    return launch_sketch_t<float>(df_dg, nm, qt0, hint, p, apply, s);
 }
 
 int band_count(int sublen, int excl) {
@@ -868,7 +880,7 @@ template <typename T>
 static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *mnc, const T *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s) {
     using T2 = typename Tr<T>::T2;
     if (p.items <= 0) return cudaSuccess;
-    if (p.seg_rows % TILE_H != 0 || p.seg_rows < 0) return cudaErrorInvalidValue;
+    if (p.seg_rows % TILE_H != 0 || p.seg_rows < 0 || p.share.n < 1 || p.share.n > MAX_PEERS) return cudaErrorInvalidValue;
     const bool carry = p.chain.log != nullptr;
     if (carry && (sizeof(T) != 8 || p.strict || p.seg_rows == 0)) return cudaErrorInvalidValue;
     const size_t smem = (size_t)cta_smem_bytes<T>();
@@ -877,7 +889,7 @@ static cudaError_t launch_tiles_t(const T *df_dg, const T *nm, const T *mnc, con
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<(unsigned)p.items, BAND_THREADS, smem, s>>>(reinterpret_cast<const T2 *>(df_dg), reinterpret_cast<const T2 *>(nm), mnc, qt0, p.series, p.mu,
-                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters, p.chain);
+                                                       prof, p.item_start, p.item_begin, p.nlb, p.n, p.m, p.sublen, p.excl, p.rank, p.world, p.seg_rows, p.counters, p.chain, p.share);
     return cudaGetLastError();
 }
 

@@ -59,7 +59,7 @@ EXPORTS = [
     "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
-    "mpb_plan_import", "mpb_plan_merge_select", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
+    "mpb_plan_import", "mpb_plan_share_thresholds", "mpb_plan_shared_with", "mpb_plan_connect_peers", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
     "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_check", "mpb_plan_timings", "mpb_plan_mu_walked", "mpb_comm_unique_id", "mpb_comm_create", "mpb_comm_destroy",
     "mpb_comm_rank", "mpb_comm_world", "mpb_plan_allreduce", "mpb_plan_compute_merged", "mpb_merge_point", "mpb_plan_total_bands",
     "mpb_plan_sketch_share", "mpb_plan_hint_device_ptr", "mpb_plan_hint_count", "mpb_plan_apply_hint", "mpb_compute_multi", "mpb_useful_cells", "mpb_measure_fma_peak",
@@ -282,9 +282,18 @@ class Plan:
     def import_(self, corr_ptr, index_ptr):
         _chk(lib().mpb_plan_import(self._h, C.c_void_p(corr_ptr), C.c_void_p(index_ptr)))
 
-    def merge_select(self, thresholds):
-        """Chain-carry mode: export / import / merge_peers address the filter thresholds (True) or the result (False)."""
-        _chk(lib().mpb_plan_merge_select(self._h, C.c_int(1 if thresholds else 0)))
+    def share_thresholds(self, others):
+        """Push this plan's profile improvements to the threshold arrays of `others` too (same process; one direction)."""
+        arr = (C.c_void_p * len(others))(*[o._h for o in others])
+        _chk(lib().mpb_plan_share_thresholds(self._h, arr, C.c_int(len(others))))
+
+    def connect_peers(self, comm):
+        """Collective: map the threshold arrays of all ranks of `comm` (P2P / CUDA IPC) and push improvements to them."""
+        _chk(lib().mpb_plan_connect_peers(self._h, comm._h))
+
+    @property
+    def shared_with(self):
+        return int(lib().mpb_plan_shared_with(self._h))
 
     def set_chain_margin(self, log2_inverse):
         _chk(lib().mpb_plan_set_chain_margin(self._h, C.c_int(log2_inverse)))
@@ -313,7 +322,7 @@ class Plan:
         return c.value
 
     def allreduce(self, comm):
-        """Exact (corr, index) max of the ranks' profiles over NCCL, in place (result, or thresholds after merge_select(True))."""
+        """Exact (corr, index) max of the ranks' result profiles over NCCL, in place (thresholds rise to the merged values)."""
         _chk(lib().mpb_plan_allreduce(self._h, comm._h))
 
     def compute_merged(self, comm):

@@ -22,6 +22,9 @@ ctx = mp.Context(local)
 comm = make_comm(ctx)
 plan = mp.Plan(ctx, n, m, dtype, 0)
 plan.set_shard(rank, world)
+if os.environ.get("MPB_TEST_NO_PEERS") is None:
+    plan.connect_peers(comm)
+    assert plan.shared_with == world - 1
 plan.upload_series(T)
 for _ in range(2):                       # twice: a second step on the same plan must give the same bits
     plan.precompute()

@@ -36,8 +36,8 @@ def single(mp, T, m, dtype=0):
 
 def test_merged_schedule_emulated_on_one_device(mp):
     """mpb_plan_compute_merged's steps with torch doing the reductions: every shard sketches its share of band 0, the hints are
-    max-reduced, the first bands are walked, the THRESHOLDS merged (merge_select), the rest walked, the RESULTS merged -- the
-    profile equals the single-plan one bit for bit (fp64 chain-carry mode)."""
+    max-reduced, the first bands are walked, the results so far merged (which lifts every shard's thresholds), the rest walked,
+    the results merged -- the profile equals the single-plan one bit for bit (fp64 chain-carry mode)."""
     import torch
     g = load_golden("walk65536_m256_w4096_t128")
     T, m = g["T"], g["m"]
@@ -69,11 +69,11 @@ def test_merged_schedule_emulated_on_one_device(mp):
             p.apply_hint()
         sub = T.size - m + 1
 
-        def merge(thresholds):
+        def merge():
             corr = [torch.empty(sub, dtype=torch.float64, device="cuda") for _ in plans]
             idx = [torch.empty(sub, dtype=torch.int32, device="cuda") for _ in plans]
             for p, c, i in zip(plans, corr, idx):
-                p.merge_select(thresholds); p.export(c.data_ptr(), i.data_ptr())
+                p.export(c.data_ptr(), i.data_ptr())
             cmax = corr[0].view(torch.int64)
             for c in corr[1:]:
                 cmax = torch.maximum(cmax, c.view(torch.int64))
@@ -85,15 +85,15 @@ def test_merged_schedule_emulated_on_one_device(mp):
                 imin = torch.minimum(imin, i)
             imin = imin.contiguous()
             for p in plans:
-                p.import_(cmax.data_ptr(), imin.data_ptr()); p.merge_select(False)
+                p.import_(cmax.data_ptr(), imin.data_ptr())
             stream.synchronize()
 
         for p in plans:
             p.compute_bands(0, pt)
-        merge(True)
+        merge()
         for p in plans:
             p.compute_bands(pt, -1)
-        merge(False)
+        merge()
         plans[1].finalize()
         stream.synchronize()
     MP, MPI, corr = plans[1].download()
@@ -101,6 +101,40 @@ def test_merged_schedule_emulated_on_one_device(mp):
         p.check(); p.close()
     ctx.close()
     assert np.array_equal(corr, corr0) and np.array_equal(MPI, MPI0) and np.array_equal(MP, MP0)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_pushed_thresholds_do_not_change_the_result(mp, dtype):
+    """Plans that push their improvements into one another's threshold arrays (what connected ranks do over NVLink; here four band
+    shards on one device, run one after the other so the later ones start from the earlier ones' thresholds) merge to the
+    single-plan profile bit for bit, with far fewer exact updates than four isolated shards."""
+    g = load_golden("walk65536_m256_w4096_t128")
+    T, m = g["T"], g["m"]
+    MP0, MPI0, corr0 = single(mp, T, m, dtype)
+    ctx = mp.Context(0)
+    world = 4
+    updates = {}
+    for shared in (False, True):
+        plans = []
+        for r in range(world):
+            p = mp.Plan(ctx, T.size, m, dtype, 0)
+            p.set_shard(r, world); p.upload_series(T); p.precompute()
+            plans.append(p)
+        if shared:
+            for p in plans:
+                p.share_thresholds([q for q in plans if q is not p])
+                assert p.shared_with == world - 1
+        for p in plans:
+            p.compute()
+        plans[0].merge_peers(plans[1:])
+        plans[0].finalize()
+        MP, MPI, corr = plans[0].download()
+        updates[shared] = sum(p.timings()["slow_updates"] for p in plans)
+        for p in plans:
+            p.check(); p.close()
+        assert np.array_equal(corr, corr0) and np.array_equal(MPI, MPI0) and np.array_equal(MP, MP0), shared
+    ctx.close()
+    assert updates[True] < 0.8 * updates[False]
 
 
 def _copy_d2d(dst, src, nbytes):
