@@ -227,6 +227,9 @@ int mpb_compute_multi(int ngpus, const int *devices, const double *T, int n, int
                       double *MP, int32_t *MPI, mpb_timings *timings);
 
 /* ---- measurement support ---- */
+/* Development aid (libraries built with -DMPB_REPLAY_HIST; all zeros otherwise): hist33[k] = replayed blocks of the last step
+ * in which k of the warp's 32 lanes passed the block filter, k = 0..32. */
+int mpb_plan_replay_histogram(mpb_plan *plan, int64_t *hist33);
 /* Register-resident DFMA (dtype MPB_F64) / FFMA (MPB_F32) issue-rate microbenchmark on ctx's device:
  * *fma_per_s = fused multiply-adds retired per second over `iters` dependent-chain iterations per thread.
  * This is the denominator of the FMA roofline. */

@@ -38,7 +38,10 @@ static_assert(sizeof(Aggregate<float>) == 8 && sizeof(InputDataPack<float>) == 1
 constexpr int DPT = MPB_DPT;              // diagonals per thread (register micro-tile width): 8 or 16
 constexpr int FWIN = 8;                   // columns a lane covers in one row
 constexpr int NWIN = DPT / FWIN;
-constexpr int RB = 8;                     // rows per branch-free block of the hot loop (one filter test per block and lane)
+#ifndef MPB_RB
+#define MPB_RB 8
+#endif
+constexpr int RB = MPB_RB;                // rows per branch-free block of the hot loop (one filter test per block and lane): 8 or 4
 constexpr int MNC_WIN = FWIN + RB - 1;    // columns a lane covers in one block = width of the staged column-window minima
 constexpr int BAND_WARPS = MPB_WARPS;     // warps per CTA
 constexpr int BAND_THREADS = 32 * BAND_WARPS;
@@ -48,6 +51,7 @@ constexpr int TILE_H = MPB_TILE_H;        // rows staged per warp tile
 constexpr int COL_WIN = TILE_H + WARP_DIAGS + DPT;   // columns (and filter-window starts) a warp tile can touch
 constexpr int COL_STRIDE = ((COL_WIN + DPT - 1) / DPT) | 1;  // entries per residue class, odd => conflict-free staging stores
 static_assert(DPT == 8 || DPT == 16, "DPT");
+static_assert(RB == 8 || RB == 4, "RB");
 static_assert(TILE_H % DPT == 0 && TILE_H % 32 == 0, "TILE_H");
 // Arrays indexed by subsequence are padded so that tiles may run past n-m+1 without bounds checks.
 constexpr int PAD = BAND_W + 4 * TILE_H + 64;

@@ -283,7 +283,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     ALLOC(p->MP, sizeof(double) * (size_t)p->sublen);
     ALLOC(p->corr, sizeof(double) * (size_t)p->sublen);
     ALLOC(p->MPI, sizeof(int32_t) * (size_t)p->sublen);
-    ALLOC(p->slow_counter, 4 * sizeof(unsigned long long));
+    ALLOC(p->slow_counter, 40 * sizeof(unsigned long long));
     ALLOC(p->hint, sizeof(int) * np);
     ALLOC(p->thr, sizeof(unsigned long long) * np);
     p->share.thr[0] = p->thr; p->share.n = 1;
@@ -298,7 +298,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     CU(cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream));
     CU(cudaMemsetAsync(p->inv, 0, es * np, c->stream));
     CU(cudaMemsetAsync(p->qt0, 0, es * np, c->stream));
-    CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(p->slow_counter, 0, 40 * sizeof(unsigned long long), c->stream));
     if (p->chain_fix) CU(cudaMemsetAsync(p->chain_stats, 0, 4 * sizeof(unsigned long long), c->stream));
     for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
     p->tm.cells = mpb_useful_cells(n, m);
@@ -450,7 +450,7 @@ int mpb_plan_local_bands(mpb_plan *p, int *count) {
 static int plan_step_begin(mpb_plan *p) {
     if (p->step_open) return MPB_OK;
     cudaStream_t s = p->ctx->stream;
-    CU(cudaMemsetAsync(p->slow_counter, 0, 4 * sizeof(unsigned long long), s));
+    CU(cudaMemsetAsync(p->slow_counter, 0, 40 * sizeof(unsigned long long), s));
     CU(cudaEventRecord(p->ev[4], s));
     p->tm.bands = p->nlb; p->tm.items = (int32_t)p->items; p->tm.segment_rows = p->seg_rows_eff;
     p->step_open = true;
@@ -735,6 +735,17 @@ int mpb_plan_mu_walked(mpb_plan *p, int *walked) {
     int bad = 0;
     CU(cudaMemcpy(&bad, (const char *)p->mu_scratch + mpb::mu_scan_bad_offset(p->n, p->m), sizeof bad, cudaMemcpyDeviceToHost));
     *walked = bad != 0;
+    return MPB_OK;
+}
+
+// development aid (builds with -DMPB_REPLAY_HIST): hist[k] = replayed blocks in which k lanes passed the block filter, k = 0..32
+int mpb_plan_replay_histogram(mpb_plan *p, int64_t *hist33) {
+    if (!p || !hist33) return fail(MPB_E_INVALID, "null argument");
+    CU(cudaSetDevice(p->ctx->device));
+    CU(cudaStreamSynchronize(p->ctx->stream));
+    unsigned long long h[40];
+    CU(cudaMemcpy(h, p->slow_counter, sizeof h, cudaMemcpyDeviceToHost));
+    for (int k = 0; k <= 32; ++k) hist33[k] = (int64_t)h[4 + k];
     return MPB_OK;
 }
 

@@ -54,7 +54,8 @@ template <typename T> struct Tr;
 template <> struct Tr<double> { using T2 = double2; };
 template <> struct Tr<float> { using T2 = float2; };
 
-static_assert(DPT == 8 && RB == DPT && NWIN == 1, "this kernel version: 8 diagonals per lane, blocks of 8 rows");
+static_assert(DPT == 8 && DPT % RB == 0 && NWIN == 1, "this kernel version: 8 diagonals per lane, blocks of 8 or 4 rows");
+constexpr int BPG = DPT / RB;             // filter blocks per group of DPT rows (one rotation of the column registers)
 constexpr int HCAP = 48;                  // hit buffer capacity (thread-rows of DPT cells)
 constexpr int HDRAIN = HCAP - 32;         // drain once more than this many thread-rows wait (a row can add up to 32)
 constexpr int SEED_KC = TILE_H;           // k-chunk of the seed dot products (series samples staged per pass)
@@ -89,7 +90,7 @@ constexpr int WCAP = MPB_WCAP;                  // winner list capacity (a drain
 template <typename T>
 struct WarpSmem {
     using T2 = typename Tr<T>::T2;
-    static constexpr int NK = (COL_STRIDE + 3) / 4 * 4;
+    static constexpr int NK = ((COL_WIN + RB - 1) / RB + 3) / 4 * 4;   // block windows start every RB columns
     static constexpr int HITS_BYTES = HCAP * DPT * (int)sizeof(T) + HCAP * 8;
     static constexpr int BYTES = ROWS_STAGED * (int)sizeof(T2) + ROWS_STAGED * 16 + COL_SLOTS * (int)sizeof(T2) + COL_SLOTS * (int)sizeof(T) + COL_SLOTS * 8 +
                                  HITS_BYTES + (ROW_BLOCKS + 1) / 2 * 2 * (int)sizeof(T2) + 2 * NK * (int)sizeof(T) + 16 + WCAP * 16 + (int)sizeof(WarpLog) + (int)((sizeof(ThrShare) + 15) / 16 * 16);
@@ -102,7 +103,7 @@ struct WarpSmem {
     int2 *hitM;       // [h] = {tile row i, window column x of its first cell}
     int *ck;          // staging scratch (aliases the empty hit buffer): [slot(x)] = filter key of best_c * norm_c
     T2 *rowK;         // [b] = minima of {best_r * norm_r * s, norm_r * s} over the rows [RB*b, RB*b + RB),  s = 1 - 2^-18
-    T *mncK;          // [q] = min of norm over the MNC_WIN columns starting at window column DPT*q
+    T *mncK;          // [q] = min of norm over the MNC_WIN columns starting at window column RB*q
     T *wK;            // [q] = min of best_c * norm_c over the same columns (key precision)
     unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] blocks replayed
     Winner *wlist;    // cells that improved the warp's view of a slot, waiting for the profile update
@@ -134,6 +135,7 @@ static_assert(COL_SLOTS * sizeof(float2) >= COL_SLOTS * sizeof(double), "seed wi
 static_assert(SEED_KC + WARP_DIAGS + DPT <= COL_WIN && SEED_KC % DPT == 0, "seed window fits the column slots");
 
 template <typename T> constexpr int cta_smem_bytes() { return BAND_WARPS * WarpSmem<T>::BYTES; }
+static_assert(4 * (BAND_WARPS * WarpSmem<double>::BYTES + 1024) <= 227 * 1024 || BAND_WARPS != 2, "four 2-warp fp64 CTAs per SM must fit the 227 KB of shared memory");
 template <typename T> constexpr int ctas_per_sm() {
     return (227 * 1024) / (cta_smem_bytes<T>() + 1024) < 1 ? 1 : ((227 * 1024) / (cta_smem_bytes<T>() + 1024) > 8 ? 8 : (227 * 1024) / (cta_smem_bytes<T>() + 1024));
 }
@@ -347,33 +349,36 @@ template <typename T> struct QVec { T v[DPT]; };
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ int hi_word(const double *p) { return reinterpret_cast<const int *>(p)[1]; }
 
-template <typename T, bool STRICT, bool LOG>
-__device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
+// PH = first row of the block inside its group of DPT rows (0, or RB when a group holds two blocks): the column registers are
+// indexed by residue class, and the class of cell j in row PH + t is (PH + t + j) mod DPT.
+template <typename T, bool STRICT, bool LOG, int PH>
+__device__ __noinline__ int replay_block(QVec<T> qc, int g0, int r0, int c0, int hitcnt, ProfileEntry *prof) {
     using T2 = typename Tr<T>::T2;
     const int lane = threadIdx.x & 31;
     WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
-    const int e0 = i0 / DPT + lane;                          // i0 is a multiple of DPT: class k of entry e0 is column i0 + DPT*lane + k
+    const int e0 = g0 / DPT + lane;                          // g0 (the group's first row) is a multiple of DPT: class k of entry e0 is column g0 + DPT*lane + k
     if (lane == 0) S.stat[2] += 1;
     T cdf[DPT], cdg[DPT], civ[DPT];
     int ckb[DPT];                                            // high word of the column's best (live view; >= 1 so that P <= 0 never passes)
 #pragma unroll
-    for (int k = 0; k < DPT; ++k) {
-        const T2 a = S.colA[k * COL_STRIDE + e0];
+    for (int k = 0; k < DPT; ++k) {                          // classes below PH already hold the next entry's column (they left the window earlier in the group)
+        const int p = k * COL_STRIDE + e0 + (k < PH ? 1 : 0);
+        const T2 a = S.colA[p];
         cdf[k] = a.x; cdg[k] = a.y;
-        civ[k] = S.colInv[k * COL_STRIDE + e0];
-        ckb[k] = max(hi_word(&S.colBest[k * COL_STRIDE + e0]), 1);
+        civ[k] = S.colInv[p];
+        ckb[k] = max(hi_word(&S.colBest[p]), 1);
     }
 #pragma unroll
     for (int t = 0; t < RB; ++t) {
-        const int i = i0 + t;
+        const int i = g0 + PH + t;
         const double2 rc = S.rowC[i];                        // {row's best, inv_r}
         const T ir = (T)rc.y;
         int kp[DPT];
         bool cand = false;
 #pragma unroll
         for (int j = 0; j < DPT; ++j) {
-            kp[j] = __double2hiint((double)corr_of(qc.v[j], ir, civ[(t + j) % DPT]));
-            cand |= kp[j] >= ckb[(t + j) % DPT];
+            kp[j] = __double2hiint((double)corr_of(qc.v[j], ir, civ[(PH + t + j) % DPT]));
+            cand |= kp[j] >= ckb[(PH + t + j) % DPT];
         }
         const int a = __vimax3_s32(kp[0], kp[1], kp[2]), b = __vimax3_s32(kp[3], kp[4], kp[5]);
         cand |= __vimax3_s32(kp[6], kp[7], max(a, b)) >= max(__double2hiint(rc.x), 1);
@@ -392,13 +397,14 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int i0, int r0, int c0, int
         }
         if (t + 1 < RB) {
             const T2 ra = S.rowA[i + 1];
-            const T2 nd = S.colA[t * COL_STRIDE + e0 + 1];   // column entering the window: i + DPT*lane + DPT
-            cdf[t] = nd.x; cdg[t] = nd.y;
-            civ[t] = S.colInv[t * COL_STRIDE + e0 + 1];
-            ckb[t] = max(hi_word(&S.colBest[t * COL_STRIDE + e0 + 1]), 1);
+            const int p = (PH + t) * COL_STRIDE + e0 + 1;    // column entering the window: g0 + PH + t + DPT*lane + DPT
+            const T2 nd = S.colA[p];
+            cdf[PH + t] = nd.x; cdg[PH + t] = nd.y;
+            civ[PH + t] = S.colInv[p];
+            ckb[PH + t] = max(hi_word(&S.colBest[p]), 1);
 #pragma unroll
             for (int j = 0; j < DPT; ++j) {
-                const int k = (t + 1 + j) % DPT;
+                const int k = (PH + t + 1 + j) % DPT;
                 qc.v[j] = qt_step<STRICT>(qc.v[j], ra.x, ra.y, cdf[k], cdg[k]);
             }
         }
@@ -563,7 +569,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
                 if (LOG) cb[k] = lower_thr(cb[k], km);
             }
 #pragma unroll
-            for (int k = 0; k < NQI; ++k) { const int q = lane + 32 * k; mq[k] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0)); }
+            for (int k = 0; k < NQI; ++k) { const int q = lane + 32 * k; mq[k] = RB * q < COL_WIN ? mnc[c0 + RB * q] : pos_inf(T(0)); }
 #pragma unroll
             for (int k = 0; k < NCI; ++k) {
                 const int x = lane + 32 * k;
@@ -590,18 +596,19 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
             S.colInv[p] = nv.y;
             S.ck[p] = nv.x < pos_inf(T(0)) ? key_of(mul_rn((T)cbest, nv.x)) : key_of(pos_inf(T(0)));   // padding: never a candidate
         }
-        for (int q = lane; q < WarpSmem<T>::NK; q += 32) S.mncK[q] = q < COL_STRIDE ? mnc[c0 + DPT * q] : pos_inf(T(0));
+        for (int q = lane; q < WarpSmem<T>::NK; q += 32) S.mncK[q] = RB * q < COL_WIN ? mnc[c0 + RB * q] : pos_inf(T(0));
 #endif
         __syncwarp();
-        // minima of the column keys over the MNC_WIN = 15 columns of each block window: lane owns window q
-        // (columns DPT*q .. DPT*q + 14 = all of entry q, classes 0..6 of entry q + 1); beyond the staged window: +inf
-        for (int q = lane; q < COL_STRIDE; q += 32) {
-            int mn = S.ck[q];
+        // minima of the column keys over the MNC_WIN columns of each block window: lane owns window q = columns
+        // [RB*q, RB*q + MNC_WIN) of the staged window (what one lane covers in one block of RB rows); beyond it: skipped
+        for (int q = lane; q < WarpSmem<T>::NK; q += 32) {
+            int mn = key_of(pos_inf(T(0)));
+            const int ph = (q % BPG) * RB, e = q / BPG;       // the window starts in class ph of entry e (ph = 0 when a group is one block)
 #pragma unroll
-            for (int k = 1; k < DPT; ++k) mn = min(mn, S.ck[k * COL_STRIDE + q]);
-            if (q + 1 < COL_STRIDE) {
-#pragma unroll
-                for (int k = 0; k < MNC_WIN - DPT; ++k) mn = min(mn, S.ck[k * COL_STRIDE + q + 1]);
+            for (int k = 0; k < MNC_WIN; ++k) {
+                const int cls = (ph + k) % DPT, ent = e + (ph + k) / DPT;
+                const int v = S.ck[cls * COL_STRIDE + min(ent, COL_STRIDE - 1)];      // branch-free: a clamped load, discarded beyond the window
+                mn = ent < COL_STRIDE ? min(mn, v) : mn;
             }
             set_key(S.wK[q], mn);
         }
@@ -616,37 +623,46 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         }
         const T2 *rowA = S.rowA + 2;                       // [ii] = {df, dg} of row i + 2 (consumed one sub-step later)
         const T2 *colA = S.colA + lane + 1;
-        const T *mncK = S.mncK + lane;                     // [I] = window terms of the block: columns [DPT*I + DPT*lane, + MNC_WIN)
-        const T *wK = S.wK + lane;
+        const T *mncK = S.mncK + BPG * lane;               // [b] = window terms of block b: columns [RB*b + DPT*lane, + MNC_WIN)
+        const T *wK = S.wK + BPG * lane;
         // operands of sub-step 0, loaded one sub-step ahead like all the others
         T2 ra = S.rowA[1];                                 // {df, dg} of row i + 1
         T2 nd = colA[0];                                   // column entering the lane's window: x = i + DPT*lane + DPT
 #pragma unroll hot_unroll<T>()
-        for (int I = 0; I < TILE_H / DPT; ++I) {
-            QVec<T> qc;                                    // QT at the start of the block (replay checkpoint)
+        for (int I = 0; I < TILE_H / DPT; ++I) {           // DPT rows: one rotation of the column registers
 #pragma unroll
-            for (int j = 0; j < DPT; ++j) qc.v[j] = qt[j];
-            const T2 rk = S.rowK[I];
-            const T cwn = mncK[I];
-            const T cww = wK[I];
-            int run = 0;
+            for (int h = 0; h < BPG; ++h) {                // RB rows: one filter test
+                QVec<T> qc;                                // QT at the start of the block (replay checkpoint)
 #pragma unroll
-            for (int ii = 0; ii < DPT; ++ii) {
-                const T2 ra_n = rowA[ii];                  // operands of sub-step ii + 1
-                const T2 nd_n = colA[((ii + 1) % DPT) * COL_STRIDE + (ii + 1) / DPT];
-                run = ii == 0 ? max_key8(qt) : max_key8(qt, run);      // keys of QT(row i)
-                cdf[ii] = nd.x; cdg[ii] = nd.y;
+                for (int j = 0; j < DPT; ++j) qc.v[j] = qt[j];
+                const T2 rk = S.rowK[I * BPG + h];
+                const T cwn = mncK[I * BPG + h];
+                const T cww = wK[I * BPG + h];
+                int run = 0;
 #pragma unroll
-                for (int j = 0; j < DPT; ++j) {
-                    const int k = (ii + 1 + j) % DPT;
-                    qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);     // QT(row i + 1)
+                for (int u = 0; u < RB; ++u) {
+                    const int ii = h * RB + u;
+                    const T2 ra_n = rowA[ii];              // operands of sub-step ii + 1
+                    const T2 nd_n = colA[((ii + 1) % DPT) * COL_STRIDE + (ii + 1) / DPT];
+                    run = u == 0 ? max_key8(qt) : max_key8(qt, run);      // keys of QT(row i)
+                    cdf[ii] = nd.x; cdg[ii] = nd.y;
+#pragma unroll
+                    for (int j = 0; j < DPT; ++j) {
+                        const int k = (ii + 1 + j) % DPT;
+                        qt[j] = qt_step<STRICT>(qt[j], ra.x, ra.y, cdf[k], cdg[k]);     // QT(row i + 1)
+                    }
+                    ra = ra_n; nd = nd_n;
                 }
-                ra = ra_n; nd = nd_n;
+                const int ka = key_of(mul_rn(rk.x, cwn));
+                const int kb = key_of(mul_rn(rk.y, cww));
+                const bool mine = run > __vimin_s32_relu(ka, kb);
+#ifdef MPB_REPLAY_HIST
+                { const unsigned bm = __ballot_sync(FULL, mine); if (bm && lane == 0 && counters) atomicAdd(counters + 4 + __popc(bm), 1ull); }
+#endif
+                if (__builtin_expect(__any_sync(FULL, mine), 0))
+                    hitcnt = h == 0 ? replay_block<T, STRICT, LOG, 0>(qc, I * DPT, r0, c0, hitcnt, prof)
+                                    : replay_block<T, STRICT, LOG, (BPG > 1 ? RB : 0)>(qc, I * DPT, r0, c0, hitcnt, prof);
             }
-            const int ka = key_of(mul_rn(rk.x, cwn));
-            const int kb = key_of(mul_rn(rk.y, cww));
-            if (__builtin_expect(__any_sync(FULL, run > __vimin_s32_relu(ka, kb)), 0))
-                hitcnt = replay_block<T, STRICT, LOG>(qc, I * DPT, r0, c0, hitcnt, prof);
             rowA += DPT; colA += 1;
         }
         if (hitcnt > 0) { drain_hits<T, LOG>(hitcnt, r0, c0, prof); hitcnt = 0; }   // candidates never outlive their tile

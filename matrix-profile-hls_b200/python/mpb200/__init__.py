@@ -60,7 +60,7 @@ EXPORTS = [
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_share_thresholds", "mpb_plan_shared_with", "mpb_plan_connect_peers", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
-    "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_check", "mpb_plan_timings", "mpb_plan_mu_walked", "mpb_comm_unique_id", "mpb_comm_create", "mpb_comm_destroy",
+    "mpb_plan_mpi_device_ptr", "mpb_plan_download_input", "mpb_plan_replay_histogram", "mpb_plan_check", "mpb_plan_timings", "mpb_plan_mu_walked", "mpb_comm_unique_id", "mpb_comm_create", "mpb_comm_destroy",
     "mpb_comm_rank", "mpb_comm_world", "mpb_plan_allreduce", "mpb_plan_compute_merged", "mpb_merge_point", "mpb_plan_total_bands",
     "mpb_plan_sketch_share", "mpb_plan_hint_device_ptr", "mpb_plan_hint_count", "mpb_plan_apply_hint", "mpb_compute_multi", "mpb_useful_cells", "mpb_measure_fma_peak",
 ]
@@ -350,6 +350,11 @@ class Plan:
         out = np.empty(self.sublen, IN_F64 if self.dtype == F64 else IN_F32)
         _chk(lib().mpb_plan_download_input(self._h, _vp(out)))
         return out
+
+    def replay_histogram(self):
+        h = (C.c_int64 * 33)()
+        _chk(lib().mpb_plan_replay_histogram(self._h, h))
+        return list(h)
 
     def check(self):
         """Waits for the plan's work; raises if the near-tie log overflowed or the corrections exceed the margin's reach."""
