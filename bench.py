@@ -196,22 +196,47 @@ def run_gpu_arm(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    n, m = args.n, args.m
+    n = args.n
     dtype = mp.F64 if args.dtype == "f64" else mp.F32
-    sublen = n - m + 1
-    cells = useful_cells(n, m)
-
     ctx = mp.Context(local)
     stream = torch.cuda.ExternalStream(ctx.stream, device=local)
-    plan = mp.Plan(ctx, n, m, dtype, 0)
-    plan.set_shard(rank, world)
-    MP_pinned = torch.empty(sublen, dtype=torch.float64).pin_memory()
-    MPI_pinned = torch.empty(sublen, dtype=torch.int32).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB of L2
     comm = None
     if world > 1:
         from mpb200.dist import make_comm
         comm = make_comm(ctx)               # communicator creation stays outside the timed region
+    fma_peak, _ = ctx.measure_fma_peak(dtype, 1 << 15)
+    fma_peak, _ = ctx.measure_fma_peak(dtype, 1 << 16)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    for m in ([int(x) for x in args.m_list.split(",")] if args.m_list else [args.m]):
+        args.m = m
+        out = bench_config(args, mp, torch, dist, ctx, stream, flush, comm, fma_peak, peaks, rank, world, local, dtype)
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+    if comm is not None:
+        comm.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def bench_config(args, mp, torch, dist, ctx, stream, flush, comm, fma_peak, peaks, rank, world, local, dtype):
+    """One (n, m) configuration: both series, device-resident and end-to-end; returns rank 0's JSON object."""
+    n, m = args.n, args.m
+    sublen = n - m + 1
+    cells = useful_cells(n, m)
+    plan = mp.Plan(ctx, n, m, dtype, 0)
+    plan.set_shard(rank, world)
+    if args.margin:
+        plan.set_chain_margin(args.margin)
+    MP_pinned = torch.empty(sublen, dtype=torch.float64).pin_memory()
+    MPI_pinned = torch.empty(sublen, dtype=torch.int32).pin_memory()
+    if world > 1:
         plan.connect_peers(comm)            # every rank maps the others' threshold arrays (CUDA IPC over NVLink), once
         ctx.finish()
 
@@ -263,21 +288,26 @@ def run_gpu_arm(args):
             dist.all_reduce(total, op=dist.ReduceOp.MAX)
         return total.item() / steps, sum(kern_ms) / len(kern_ms), launches, clocks, tm
 
-    fma_peak, _ = ctx.measure_fma_peak(dtype, 1 << 15)
-    fma_peak, _ = ctx.measure_fma_peak(dtype, 1 << 16)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except OSError:
-        pass
-
     def measure(kind):
         T_pinned = torch.from_numpy(synth_series(n, kind)).pin_memory()
         plan.upload_series_ptr(T_pinned.data_ptr())
         ctx.finish()
         ms_dev, band_ms, launches, clocks, tm = timed(False, args.steps, args.warmup, T_pinned)
         ms_e2e, _, _, clocks_e2e, _ = timed(True, args.steps, max(3, args.warmup // 2), T_pinned)
-        plan.check()                                        # every rank: the chain-carry margin covered what it had to (raises otherwise)
+        bad = 0                                             # every rank: the chain-carry margin covered what it had to
+        try:
+            plan.check()
+        except mp.MpbError as e:
+            if e.code != -5:                                # MPB_E_MARGIN: measure again with a wider margin (all ranks together)
+                raise
+            bad = 1
+        if world > 1:
+            flag = torch.tensor([bad], dtype=torch.int32, device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+            bad = int(flag.item())
+        if bad:
+            import math
+            return -int(round(math.log2(plan.timings()["chain_margin"])))
         one_call_ms = None
         if world == 1 and rank == 0:                        # mpb_compute itself: pageable host buffers, plan create / destroy inside
             Tn = T_pinned.numpy().copy()
@@ -313,9 +343,16 @@ def run_gpu_arm(args):
                 "counters": {k: tm[k] for k in ("slow_updates", "filter_hits", "replays", "cells_walked", "reseeded_diagonals", "chain_candidates",
                                                 "chain_max_correction", "chain_bound", "chain_margin", "items", "segment_rows", "bands")}}
 
-    head = measure(args.data)
+    def measure_with_margin(kind):
+        while True:
+            res = measure(kind)
+            if not isinstance(res, int):
+                return res
+            plan.set_chain_margin(max(8, res - 2))          # res = the margin's log2 that proved too narrow
+
+    head = measure_with_margin(args.data)
     other = "uniform" if args.data == "walk" else "walk"
-    second = measure(other) if not args.no_second_series else None
+    second = measure_with_margin(other) if not args.no_second_series else None
     out = None
     if rank == 0:
         out = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -326,19 +363,12 @@ def run_gpu_arm(args):
             second["config"] = workload_config(args, other)
             out["tsb_shaped" if other == "uniform" else "random_walk"] = second
     plan.close()
-    if comm is not None:
-        comm.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu_reference_sample(n, m, args.data, target_s=1.0)          # pages the library and the series in (untimed)
         cb = cpu_reference_sample(n, m, args.data, target_s=args.ref_seconds)
         cb.pop("seconds", None)
         out["cpu_baseline"] = cb
-    if rank == 0:
-        print(json.dumps(out), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    return 0
+    return out
 
 
 def main():
@@ -354,6 +384,8 @@ def main():
     ap.add_argument("--ref-seconds", type=float, default=12.0, help="CPU seconds per reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-second-series", action="store_true", help="skip the second series block (long configs)")
+    ap.add_argument("--m-list", default="", help="comma list of subsequence lengths: one JSON line per m (BASELINE.json config 5)")
+    ap.add_argument("--margin", type=int, default=0, help="chain-carry near-tie margin 2^-k (0 = the library's default for n)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -73,7 +73,7 @@ cudaError_t launch_merge_peer(ProfileEntry *prof, const ProfileEntry *peer, int 
 // chunk-compatible MatrixProfileKernelTLF: chunk_tlf.cu
 cudaError_t launch_chunk_tlf_f64(int n, int m, int w, int iteration, const void *input, void *output, void *scratch, size_t scratch_bytes, cudaStream_t s);
 cudaError_t launch_chunk_tlf_f32(int n, int m, int w, int iteration, const void *input, void *output, void *scratch, size_t scratch_bytes, cudaStream_t s);
-size_t chunk_tlf_scratch_bytes(int n, int m);
+size_t chunk_tlf_scratch_bytes(int n, int m, int w);
 
 // measurement: peak_fma.cu
 cudaError_t launch_fma_peak(int dtype, int iters, int blocks, double *sink, cudaStream_t s);

@@ -192,7 +192,7 @@ int mpb_kernel_tlf_enqueue(mpb_context *c, int dtype, int n, int m, int w, int i
     const size_t nRows = sublen - (size_t)iteration * w;
     if (output->bytes < nRows * esz) return fail(MPB_E_INVALID, "output buffer holds %zu bytes, need %zu", output->bytes, nRows * esz);
     CU(cudaSetDevice(c->device));
-    const size_t need = mpb::chunk_tlf_scratch_bytes(n, m);
+    const size_t need = mpb::chunk_tlf_scratch_bytes(n, m, w);
     if (c->tlf_scratch_bytes < need) {
         CU(cudaStreamSynchronize(c->stream));
         if (c->tlf_scratch) cudaFree(c->tlf_scratch);

@@ -525,3 +525,32 @@ def test_running_mean_scan_equals_the_walk(mp, ctx, kind, n, m):
         assert walked == bool(flags & mp.FLAG_MU_WALK)
         plan.close()
     assert packs[0].tobytes() == packs[1].tobytes()
+
+
+def test_tlf_chunks_at_w4096_n65536(mp, oracle):
+    """MatrixProfileKernelTLF at the reference README's chunk width (w = 4096) on the n = 65536 random-walk golden: three chunks
+    byte-for-byte against the CPU restatement of the Vanilla kernel, and the reference's host flow over ALL 16 chunks
+    (UpdateAggregates + PostComputeAggregates, host/MatrixProfileHost.cpp:101-142) bit-equal to the golden merged profile."""
+    g = load_golden("walk65536_m256_w4096_t128")
+    T, m, w = g["T"], g["m"], 4096
+    n = T.size
+    sublen = n - m + 1
+    inp = oracle.precompute(T, m)
+    out = np.zeros(sublen, mp.OUT_F64)
+    nit = (n - m + w) // w
+    rv = np.full(sublen, -1e12); ri = np.full(sublen, -1, np.int32)
+    cv = np.full(sublen, -1e12); ci = np.full(sublen, -1, np.int32)
+    for it in range(nit):
+        mp.MatrixProfileKernelTLF(n, m, it, inp, out, w=w)
+        off, nr = it * w, sublen - it * w
+        if it in (0, 7, nit - 1):
+            want = oracle.kernel("vanilla", n, m, w, it, inp)
+            for agg in ("rowAggregate", "columnAggregate"):          # field bytes (the struct padding is not part of the contract)
+                assert np.array_equal(out[agg]["value"][:nr], want[agg]["value"][:nr]), (it, agg)
+                assert np.array_equal(out[agg]["index"][:nr], want[agg]["index"][:nr]), (it, agg)
+        a, b = out["rowAggregate"][:nr], out["columnAggregate"][:nr]
+        k = a["value"] > rv[:nr]; rv[:nr][k] = a["value"][k]; ri[:nr][k] = a["index"][k]
+        k = b["value"] > cv[off:]; cv[off:][k] = b["value"][k]; ci[off:][k] = b["index"][k]
+    pick = rv > cv
+    assert np.array_equal(np.where(pick, rv, cv), g["vanilla_corr"])
+    assert np.array_equal(np.where(pick, ri, ci), g["vanilla_MPI"])
