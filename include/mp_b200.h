@@ -96,6 +96,18 @@ size_t mpb_buffer_size(mpb_buffer *buf);
  * (OpenCL.hpp:246-267, 379-381; call sites host/MatrixProfileHost.cpp:110-113). Asynchronous. */
 int mpb_kernel_tlf_enqueue(mpb_context *ctx, int dtype, int n, int m, int w, int iteration,
                            const mpb_buffer *input, mpb_buffer *output);
+/* Allocation-free variant of mpb_kernel_tlf_enqueue.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same bytes written.  The chunk's work space -- 32 bytes per subsequence + 8*w bytes per 192 rows -- is a
+ * file-scope __device__ array of MPB_TLF_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; a problem
+ * that needs more is rejected with MPB_E_INVALID (n = 65536, m = 256 at w = 4096 needs 12.6 MiB; n = 2^20 does not fit).
+ * The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine (the first call on a device looks
+ * the array's address up with cudaGetSymbolAddress: make that one outside a graph capture).  All calls share the one array
+ * and it keeps the previous call's contents: what must start at zero is cleared by the call itself, and two calls that
+ * overlap on the GPU (different streams / contexts of one device) race -- serialise them. */
+#define MPB_TLF_NOALLOC_SCRATCH_BYTES (16u << 20)
+int mpb_kernel_tlf_enqueue_noalloc(mpb_context *ctx, int dtype, int n, int m, int w, int iteration,
+                                   const mpb_buffer *input, mpb_buffer *output);
 /* Host-pointer form of the same contract (what a MatrixProfileKernel<data_t,int,w> subclass calls):
  * copies input (n-m+1 InputDataPacks) to the device, runs the chunk, copies back nRows OutputDataPacks. */
 int mpb_kernel_tlf_f64(int n, int m, int w, int iteration, const void *input, void *output);

@@ -10,6 +10,9 @@
 // This is the drop-in/compat path (bit-for-bit the reference kernel's OutputDataPacks); the fast path is scamp_tile.cu.
 #include "mp_common.cuh"
 #include "mp_kernels.h"
+#include "mp_runtime.h"
+
+#include <mutex>
 
 namespace mpb {
 
@@ -212,3 +215,57 @@ cudaError_t launch_chunk_tlf_f32(int n, int m, int w, int iteration, const void 
 }
 
 }  // namespace mpb
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of mpb_kernel_tlf_enqueue (include/mp_b200.h: no counterpart in the reference; added
+// for callers that cannot call cudaMalloc -- CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The chunk's work space (running (value, tie) pairs + chain checkpoints) lives in ONE file-scope device array
+// of MPB_TLF_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  In host code the array's name is
+// only a host-side stand-in: its device address is taken once per device with cudaGetSymbolAddress (that device current)
+// and that pointer is what the kernels receive.  All calls share the array: tlf_init_kernel clears the pairs of the chunk's
+// rows at the start of every call (the checkpoints are written before they are read), and calls that overlap on the GPU
+// (two streams, two contexts of one device) race on it.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_tlf_static_scratch[MPB_TLF_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void *g_static_addr[kMaxDevices] = {};      // device address of g_tlf_static_scratch, per device ordinal
+
+// device must be current
+cudaError_t tlf_static_scratch(int device, void **ptr) {
+    std::lock_guard<std::mutex> l(g_static_mu);
+    if (!g_static_addr[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_tlf_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_addr[device] = p;
+    }
+    *ptr = g_static_addr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int mpb_kernel_tlf_enqueue_noalloc(mpb_context *c, int dtype, int n, int m, int w, int iteration, const mpb_buffer *input, mpb_buffer *output) {
+    if (!c || !input || !output) return fail(MPB_E_INVALID, "null argument");
+    if (dtype != MPB_F64 && dtype != MPB_F32) return fail(MPB_E_INVALID, "dtype must be MPB_F64 or MPB_F32");
+    if (m < 4 || n < m) return fail(MPB_E_INVALID, "need n >= m >= 4 (n=%d, m=%d)", n, m);
+    if (w < 8 || w > n || w >= (1 << 24)) return fail(MPB_E_INVALID, "need 8 <= w <= n (w=%d)", w);
+    if (iteration < 0 || (long long)iteration * w >= (long long)(n - m + 1)) return fail(MPB_E_INVALID, "iteration %d outside [0, ceil((n-m+1)/w))", iteration);
+    const size_t need = mpb::chunk_tlf_scratch_bytes(n, m, w);
+    if (need > (size_t)MPB_TLF_NOALLOC_SCRATCH_BYTES)
+        return fail(MPB_E_INVALID, "mpb_kernel_tlf_enqueue_noalloc: n=%d, m=%d, w=%d needs %zu bytes of work space, the static array holds %zu "
+                                   "(MPB_TLF_NOALLOC_SCRATCH_BYTES); use mpb_kernel_tlf_enqueue for larger problems", n, m, w, need, (size_t)MPB_TLF_NOALLOC_SCRATCH_BYTES);
+    const size_t sublen = (size_t)(n - m + 1), esz = dtype == MPB_F64 ? 32 : 16;
+    if (input->bytes < sublen * esz) return fail(MPB_E_INVALID, "input buffer holds %zu bytes, need %zu", input->bytes, sublen * esz);
+    const size_t nRows = sublen - (size_t)iteration * w;
+    if (output->bytes < nRows * esz) return fail(MPB_E_INVALID, "output buffer holds %zu bytes, need %zu", output->bytes, nRows * esz);
+    if (c->device < 0 || c->device >= kMaxDevices) return fail(MPB_E_INVALID, "device ordinal %d beyond the %d this entry point tracks", c->device, kMaxDevices);
+    CU(cudaSetDevice(c->device));
+    void *scratch = nullptr;
+    CU(tlf_static_scratch(c->device, &scratch));
+    if (dtype == MPB_F64) CU(mpb::launch_chunk_tlf_f64(n, m, w, iteration, input->ptr, output->ptr, scratch, MPB_TLF_NOALLOC_SCRATCH_BYTES, c->stream));
+    else CU(mpb::launch_chunk_tlf_f32(n, m, w, iteration, input->ptr, output->ptr, scratch, MPB_TLF_NOALLOC_SCRATCH_BYTES, c->stream));
+    return MPB_OK;
+}

@@ -57,7 +57,7 @@ template <typename H> void reg_add(std::set<H *> &set, H *h) { std::lock_guard<s
 extern "C" {
 
 const char *mpb_last_error(void) { return g_err; }
-const char *mpb_version(void) { return "mpb200 0.4 (sm_100a; tile kernel: 8 diagonals per lane, 512-diagonal bands, per-warp tiles of 128 rows, block-wide QT-domain filter, re-seeded row segments)"; }
+const char *mpb_version(void) { return "mpb200 0.5 (sm_100a; tile kernel: 8 diagonals per lane, 512-diagonal bands, per-warp tiles of 192 rows, block-wide QT-domain filter, (band x row segment) work items, fp64 chain carry, NCCL merge)"; }
 
 int mpb_device_count(int *count) {
     if (!count) return fail(MPB_E_INVALID, "count is null");

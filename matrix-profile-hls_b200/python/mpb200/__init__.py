@@ -22,6 +22,7 @@ import numpy as np
 F64, F32 = 0, 1
 FLAG_STRICT, FLAG_SEQ_MEAN, FLAG_NO_RESEED, FLAG_NO_SEED, FLAG_NO_CHAIN_CARRY, FLAG_WINDOW_MEAN, FLAG_MU_WALK = 1, 2, 4, 8, 16, 32, 64
 _LIB = None
+TLF_NOALLOC_SCRATCH_BYTES = 16 << 20     # MPB_TLF_NOALLOC_SCRATCH_BYTES (include/mp_b200.h)
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # matrix-profile-hls_b200/
 LIB_PATH = os.environ.get("MPB200_LIB") or os.path.join(_PKG_ROOT, "libmpb200.so")   # MPB200_LIB: tuning builds (csrc/Makefile VARIANT=)
 
@@ -56,7 +57,7 @@ class Timings(C.Structure):
 EXPORTS = [
     "mpb_last_error", "mpb_version", "mpb_device_count", "mpb_context_create", "mpb_context_destroy", "mpb_context_finish",
     "mpb_context_stream", "mpb_context_device", "mpb_buffer_create", "mpb_buffer_destroy", "mpb_buffer_copy_from_host",
-    "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_f64",
+    "mpb_buffer_copy_to_host", "mpb_buffer_device_ptr", "mpb_buffer_size", "mpb_kernel_tlf_enqueue", "mpb_kernel_tlf_enqueue_noalloc", "mpb_kernel_tlf_f64",
     "mpb_kernel_tlf_f32", "mpb_compute", "mpb_plan_create", "mpb_plan_destroy", "mpb_plan_set_shard", "mpb_plan_set_segment_rows", "mpb_plan_segment_rows", "mpb_plan_set_sketch_bands", "mpb_plan_upload_series",
     "mpb_plan_series_device_ptr", "mpb_plan_precompute", "mpb_plan_compute", "mpb_plan_compute_bands", "mpb_plan_local_bands", "mpb_plan_export", "mpb_plan_mask_index",
     "mpb_plan_import", "mpb_plan_share_thresholds", "mpb_plan_shared_with", "mpb_plan_connect_peers", "mpb_plan_set_chain_margin", "mpb_plan_set_log_entries", "mpb_plan_merge_peers", "mpb_plan_finalize", "mpb_plan_download", "mpb_plan_mp_device_ptr",
@@ -141,6 +142,12 @@ class Context:
 
     def make_buffer(self, nbytes):
         return Buffer(self, nbytes)
+
+    def kernel_tlf_enqueue(self, dtype, n, m, w, iteration, input_buf, output_buf, *, noalloc=False):
+        """Kernel::EnqueueTask() of the chunk kernel on device buffers (asynchronous).  noalloc=True takes the entry point whose
+        work space is the library's static device array (no cudaMalloc inside; size limit TLF_NOALLOC_SCRATCH_BYTES)."""
+        fn = lib().mpb_kernel_tlf_enqueue_noalloc if noalloc else lib().mpb_kernel_tlf_enqueue
+        _chk(fn(self._h, C.c_int(dtype), C.c_int(n), C.c_int(m), C.c_int(w), C.c_int(iteration), input_buf._h, output_buf._h))
 
     def measure_fma_peak(self, dtype=F64, iters=1 << 15):
         r, ms = C.c_double(0), C.c_double(0)
