@@ -171,7 +171,7 @@ def workload_config(args, kind):
 
 def executed_pipe_ops(tm, m, sketch_cells):
     """FP64/FP32-pipe operations the step EXECUTES, from the kernel's own counters:
-    hot loop 128 FMA + 2 MUL per 64-cell block of every walked cell; a replayed block (8 rows x 8 diagonals x 32 lanes) walks its
+    hot loop 128 FMA + 2 MUL per 64-cell block of every walked cell; a replay pass (32 lanes, one queued 8 x 8-cell block each) walks
     2048 cells again with 2 FMA + 2 MUL each; a parked cell costs 2 MUL in the drain; a re-seeded diagonal m FMA; a sketched cell
     2 FMA + 2 MUL."""
     return (tm["cells_walked"] * (130.0 / 64.0) + tm["replays"] * 2048 * 4.0 + tm["filter_hits"] * 8 * 2.0
@@ -340,7 +340,7 @@ def bench_config(args, mp, torch, dist, ctx, stream, flush, comm, fma_peak, peak
                              "hbm": {"algorithmic_bytes_per_step": hbm_alg, "achieved_gbs": hbm_alg / (band_ms * 1e-3) / 1e9,
                                      "peak_gbs": peaks.get("hbm_gbs", 6650.0), "peak_source": "measured" if peaks else "fallback"}},
                 "clocks": clocks, "phases_ms": {k: tm[k] for k in ("precompute_ms", "compute_ms", "finalize_ms")},
-                "counters": {k: tm[k] for k in ("slow_updates", "filter_hits", "replays", "cells_walked", "reseeded_diagonals", "chain_candidates",
+                "counters": {k: tm[k] for k in ("slow_updates", "filter_hits", "replays", "replay_lane_blocks", "cells_walked", "reseeded_diagonals", "chain_candidates",
                                                 "chain_max_correction", "chain_bound", "chain_margin", "items", "segment_rows", "bands")}}
 
     def measure_with_margin(kind):

@@ -126,7 +126,7 @@ typedef struct {
     int32_t items;        /* (band, row segment) work items = CTAs of the tile kernel */
     int32_t segment_rows; /* rows per re-seeded segment (0 = full-length chains) */
     int64_t filter_hits;  /* cells that passed the QT-domain filter and were checked exactly against the profile */
-    int64_t replays;      /* 8-row x 8-diagonal x 32-lane blocks walked a second time because a cell in them passed the block filter */
+    int64_t replays;      /* replay passes: 32 lanes x (8 rows x 8 diagonals) walked a second time in the per-cell form (one queued lane-block per lane) */
     int64_t chain_candidates;    /* chain-carry mode: values (slot entries + logged near ties) resolved with their carry */
     double chain_max_correction; /* chain-carry mode: largest relative correction |carry * inv_r * inv_c| / P applied (how far the
                                     independent segments were from the unbroken chain); 0 in the other modes */
@@ -134,6 +134,7 @@ typedef struct {
     double chain_margin;         /* chain-carry mode: the near-tie margin in effect (relative) */
     int64_t cells_walked;        /* cells this rank's tile kernel walks (useful cells + exclusion-free padding of the last tiles / bands) */
     int64_t reseeded_diagonals;  /* (diagonal, segment) pairs that start from an exact dot product of m terms */
+    int64_t replay_lane_blocks;  /* (lane, 8 x 8-cell block) pairs that passed the block filter and were queued for a replay pass */
 } mpb_timings;
 
 /* One-call form with HOST buffers (copies inside): T[n] float64 in; MP[n-m+1] float64 (z-normalised

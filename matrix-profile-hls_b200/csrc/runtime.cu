@@ -770,6 +770,7 @@ int mpb_plan_timings(mpb_plan *p, mpb_timings *out) {
     t.filter_hits = (int64_t)cnt[0];
     t.slow_updates = (int64_t)cnt[1];
     t.replays = (int64_t)cnt[2];
+    t.replay_lane_blocks = (int64_t)cnt[3];
     t.chain_candidates = 0; t.chain_max_correction = 0.0; t.chain_bound = 0.0; t.chain_margin = 0.0;
     if (p->chain_fix) {
         unsigned long long st[4] = {0, 0, 0, 0};

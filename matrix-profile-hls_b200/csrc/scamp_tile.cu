@@ -105,7 +105,7 @@ struct WarpSmem {
     T2 *rowK;         // [b] = minima of {best_r * norm_r * s, norm_r * s} over the rows [RB*b, RB*b + RB),  s = 1 - 2^-18
     T *mncK;          // [q] = min of norm over the MNC_WIN columns starting at window column RB*q
     T *wK;            // [q] = min of best_c * norm_c over the same columns (key precision)
-    unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] blocks replayed
+    unsigned *stat;   // [0] thread-rows parked, [1] profile slots improved, [2] replay passes (32 lane-blocks wide), [3] lane-blocks queued for the replay
     Winner *wlist;    // cells that improved the warp's view of a slot, waiting for the profile update
     WarpLog *wlog;    // chain-carry mode: where this warp appends its candidates
     ThrShare *wsh;    // the job's threshold arrays (own + peers): where improvements are pushed
@@ -413,6 +413,89 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int g0, int r0, int c0, int
 }
 
 // ---------------------------------------------------------------------------------------------
+// Deferred, lane-compacted replay (RB == DPT builds).  On smooth series the block filter is loose: a fifth of the
+// (warp, block) pairs have SOME lane passing, but only ~1 lane in 32 does (scripts/filter_sim.py; 70 % of the warp-wide
+// replays parked nothing), so a warp-wide replay spends 31 lanes on blocks that did not pass.  Instead, a lane whose block
+// passes only QUEUES it -- the block's starting QT values and its position, in the (empty) hit buffer -- and carries on.
+// When QCAP lane-blocks wait, or at the end of the tile, the warp replays the queue with ONE QUEUED BLOCK PER LANE: the
+// same walk as replay_block (same operands, same order, bit-identical QT; every cell's P = (QT * inv_r) * inv_c compared
+// by its high word with the warp's view of the column's and the row's best), only that row and column positions now
+// differ from lane to lane.  Blocks start at multiples of DPT rows, so the residue class of cell j in row t is (t + j)
+// mod DPT in every lane and the column registers rotate statically, as in the hot loop.  The entries are in registers
+// before the first thread-row is parked, so the queue and the hit buffer share their storage.
+// Warp-collective; leaves the hit buffer drained.
+// ---------------------------------------------------------------------------------------------
+constexpr int QCAP = 32;                  // queued lane-blocks replayed in one pass
+template <typename T, bool STRICT, bool LOG>
+__device__ __noinline__ void flush_queue(int qcount, int r0, int c0, ProfileEntry *prof) {
+    using T2 = typename Tr<T>::T2;
+    const int lane = threadIdx.x & 31;
+    WarpSmem<T> S(smem_raw + (threadIdx.x >> 5) * WarpSmem<T>::BYTES);
+    __syncwarp();
+    const bool act = lane < qcount;
+    const int2 q = act ? S.hitM[lane] : make_int2(0, 0);     // {first row of the block (tile row, multiple of DPT), window column of its first cell}
+    const int i0 = q.x, e0 = q.y / DPT;
+    T qc[DPT];
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) qc[j] = act ? S.hitQ[lane * DPT + j] : T(0);
+    if (lane == 0) S.stat[2] += 1;
+    __syncwarp();                                            // every entry is in registers: the buffer now takes parked thread-rows
+    int hitcnt = 0;
+    T cdf[DPT], cdg[DPT], civ[DPT];
+    int ckb[DPT];                                            // high word of the column's best (live view; >= 1 so that P <= 0 never passes)
+#pragma unroll
+    for (int k = 0; k < DPT; ++k) {
+        const int p = k * COL_STRIDE + e0;
+        const T2 a = S.colA[p];
+        cdf[k] = a.x; cdg[k] = a.y;
+        civ[k] = S.colInv[p];
+        ckb[k] = max(hi_word(&S.colBest[p]), 1);
+    }
+#pragma unroll
+    for (int t = 0; t < RB; ++t) {
+        const int i = i0 + t;
+        const double2 rc = S.rowC[i];                        // {row's best, inv_r}
+        const T ir = (T)rc.y;
+        int kp[DPT];
+        bool cand = false;
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {
+            kp[j] = __double2hiint((double)corr_of(qc[j], ir, civ[(t + j) % DPT]));
+            cand |= kp[j] >= ckb[(t + j) % DPT];
+        }
+        const int a = __vimax3_s32(kp[0], kp[1], kp[2]), b = __vimax3_s32(kp[3], kp[4], kp[5]);
+        cand |= __vimax3_s32(kp[6], kp[7], max(a, b)) >= max(__double2hiint(rc.x), 1);
+        cand &= act;
+        const unsigned mk = __ballot_sync(FULL, cand);
+        if (mk) {
+            if (cand) {
+                const int pos = hitcnt + __popc(mk & ((1u << lane) - 1u));
+#pragma unroll
+                for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = qc[j];
+                S.hitM[pos] = make_int2(i, q.y + t);
+            }
+            hitcnt += __popc(mk);
+            if (hitcnt > HDRAIN) { drain_hits<T, LOG>(hitcnt, r0, c0, prof); hitcnt = 0; }
+        }
+        if (t + 1 < RB) {
+            const T2 ra = S.rowA[i + 1];
+            const int p = t * COL_STRIDE + e0 + 1;           // column entering the lane's window
+            const T2 nd = S.colA[p];
+            cdf[t] = nd.x; cdg[t] = nd.y;
+            civ[t] = S.colInv[p];
+            ckb[t] = max(hi_word(&S.colBest[p]), 1);
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                const int k = (t + 1 + j) % DPT;
+                qc[j] = qt_step<STRICT>(qc[j], ra.x, ra.y, cdf[k], cdg[k]);
+            }
+        }
+    }
+    if (hitcnt > 0) drain_hits<T, LOG>(hitcnt, r0, c0, prof);
+    __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
 // Exact re-seed of this lane's DPT diagonals at row rs (segment start - 1), in fp64 from the series:
 //   QT(rs, c) = sum_k A[k] * (T[c+k] - mu_ref) - (mu_c - mu_ref) * sum_k A[k],   A[k] = T[rs+k] - mu_rs,
 // algebraically sum_k (T[rs+k]-mu_rs)(T[c+k]-mu_c) (include/host/HostSideComputation.hpp:37 generalised from
@@ -492,7 +575,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
         reseed<T>(qt, S, Tser, mu, n, m, sublen, rbeg - 1, d0w, lane);
     }
 
-    int hitcnt = 0;                 // warp-uniform: hits parked in the buffer
+    int hitcnt = 0;                 // warp-uniform: lane-blocks queued for the replay (BPG == 1) / thread-rows parked (BPG > 1)
     if (lane < 4) S.stat[lane] = 0;
     if (lane == 0) {
 #pragma unroll
@@ -659,13 +742,32 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
 #ifdef MPB_REPLAY_HIST
                 { const unsigned bm = __ballot_sync(FULL, mine); if (bm && lane == 0 && counters) atomicAdd(counters + 4 + __popc(bm), 1ull); }
 #endif
-                if (__builtin_expect(__any_sync(FULL, mine), 0))
-                    hitcnt = h == 0 ? replay_block<T, STRICT, LOG, 0>(qc, I * DPT, r0, c0, hitcnt, prof)
-                                    : replay_block<T, STRICT, LOG, (BPG > 1 ? RB : 0)>(qc, I * DPT, r0, c0, hitcnt, prof);
+                if (__builtin_expect(__any_sync(FULL, mine), 0)) {
+                    if constexpr (BPG == 1) {                  // queue the lane-blocks that passed (flush_queue replays them one per lane)
+                        const unsigned bm = __ballot_sync(FULL, mine);
+                        const int nq = __popc(bm);
+                        if (hitcnt + nq > QCAP) { flush_queue<T, STRICT, LOG>(hitcnt, r0, c0, prof); hitcnt = 0; }
+                        if (mine) {
+                            const int pos = hitcnt + __popc(bm & ((1u << lane) - 1u));
+#pragma unroll
+                            for (int j = 0; j < DPT; ++j) S.hitQ[pos * DPT + j] = qc.v[j];
+                            S.hitM[pos] = make_int2(I * DPT, I * DPT + DPT * lane);
+                        }
+                        if (lane == 0) S.stat[3] += nq;
+                        hitcnt += nq;
+                    } else {
+                        hitcnt = h == 0 ? replay_block<T, STRICT, LOG, 0>(qc, I * DPT, r0, c0, hitcnt, prof)
+                                        : replay_block<T, STRICT, LOG, (BPG > 1 ? RB : 0)>(qc, I * DPT, r0, c0, hitcnt, prof);
+                    }
+                }
             }
             rowA += DPT; colA += 1;
         }
-        if (hitcnt > 0) { drain_hits<T, LOG>(hitcnt, r0, c0, prof); hitcnt = 0; }   // candidates never outlive their tile
+        if (hitcnt > 0) {                                  // candidates never outlive their tile
+            if constexpr (BPG == 1) flush_queue<T, STRICT, LOG>(hitcnt, r0, c0, prof);
+            else drain_hits<T, LOG>(hitcnt, r0, c0, prof);
+            hitcnt = 0;
+        }
     }
     if (LOG) {                                             // E_k: the chain's value at the first row of the next segment
         const int item_e = blockIdx.x + item_begin;
@@ -676,7 +778,7 @@ tile_kernel(const typename Tr<T>::T2 *__restrict__ df_dg, const typename Tr<T>::
     __syncwarp();
     if (counters && lane == 0 && S.stat[2]) {
         atomicAdd(counters, (unsigned long long)S.stat[0]); atomicAdd(counters + 1, (unsigned long long)S.stat[1]);
-        atomicAdd(counters + 2, (unsigned long long)S.stat[2]);
+        atomicAdd(counters + 2, (unsigned long long)S.stat[2]); atomicAdd(counters + 3, (unsigned long long)S.stat[3]);
     }
 }
 

@@ -48,7 +48,7 @@ class Timings(C.Structure):
                 ("d2h_ms", C.c_double), ("total_ms", C.c_double), ("cells", C.c_int64), ("slow_updates", C.c_int64),
                 ("launches", C.c_int32), ("bands", C.c_int32), ("items", C.c_int32), ("segment_rows", C.c_int32), ("filter_hits", C.c_int64), ("replays", C.c_int64),
                 ("chain_candidates", C.c_int64), ("chain_max_correction", C.c_double), ("chain_bound", C.c_double), ("chain_margin", C.c_double),
-                ("cells_walked", C.c_int64), ("reseeded_diagonals", C.c_int64)]
+                ("cells_walked", C.c_int64), ("reseeded_diagonals", C.c_int64), ("replay_lane_blocks", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -26,7 +26,7 @@ for n in sizes:
                 best = t if best is None or t["compute_ms"] < best["compute_ms"] else best
             print(json.dumps({"variant": os.environ.get("MPB_VARIANT"), "n": n, "data": kind, "dtype": name, "compute_ms": round(best["compute_ms"], 3),
                               "pre_ms": round(best["precompute_ms"], 3), "cells_per_s": best["cells"] / (best["compute_ms"] * 1e-3),
-                              "hits": best["filter_hits"], "wins": best["slow_updates"], "replays": best["replays"], "items": best["items"], "seg_rows": best["segment_rows"],
+                              "hits": best["filter_hits"], "wins": best["slow_updates"], "replays": best["replays"], "queued": best["replay_lane_blocks"], "items": best["items"], "seg_rows": best["segment_rows"],
                               "mp_sum": float(MP.sum()), "mpi_sum": int(MPI.astype(np.int64).sum())}), flush=True)
             plan.close()
 ''' % PKG
