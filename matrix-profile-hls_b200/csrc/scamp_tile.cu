@@ -414,7 +414,7 @@ __device__ __noinline__ int replay_block(QVec<T> qc, int g0, int r0, int c0, int
 
 // ---------------------------------------------------------------------------------------------
 // Deferred, lane-compacted replay (RB == DPT builds).  On smooth series the block filter is loose: a fifth of the
-// (warp, block) pairs have SOME lane passing, but only ~1 lane in 32 does (scripts/filter_sim.py; 70 % of the warp-wide
+// (warp, block) pairs have SOME lane passing, but only ~1 lane in 32 does (tests/tools/filter_sim.py; 70 % of the warp-wide
 // replays parked nothing), so a warp-wide replay spends 31 lanes on blocks that did not pass.  Instead, a lane whose block
 // passes only QUEUES it -- the block's starting QT values and its position, in the (empty) hit buffer -- and carries on.
 // When QCAP lane-blocks wait, or at the end of the tile, the warp replays the queue with ONE QUEUED BLOCK PER LANE: the

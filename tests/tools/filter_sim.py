@@ -1,5 +1,7 @@
+"""CPU analysis tool (not a test, not product code): pass rates of the tile kernel's block filter and of tighter variants on a synthetic series,
+with the final profile as the thresholds.  usage: python tests/tools/filter_sim.py [n] [m] [walk|uniform]"""
 import sys, os, numpy as np, time
-sys.path.insert(0, '/root/repo/oracle')
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..', '..', 'oracle'))   # the oracle is test infrastructure: this analysis tool lives under tests/
 from oracle_py import Oracle, random_walk
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 16
 m = int(sys.argv[2]) if len(sys.argv) > 2 else 256
