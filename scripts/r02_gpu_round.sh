@@ -13,7 +13,7 @@ timeout 600 python bench.py --steps 5 --warmup 3 > $o/${tag}_bench.json 2> $o/${
 timeout 300 python bench.py --impl reference --steps 1 --warmup 1 > $o/${tag}_bench_reference_arm.json 2>> $o/${tag}_bench.err
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches_walk.csv \
     python scripts/profile_one.py 1048576 256 f64 walk > $o/${tag}_ncu_launches.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:tile_kernel --launch-skip 2 -c 1 -f -o $o/${tag}_tile_walk \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:tile_kernel --launch-skip 1 -c 1 -f -o $o/${tag}_tile_walk \
     python scripts/profile_one.py 1048576 256 f64 walk > $o/${tag}_ncu_full.log 2>&1
 ncu -i $o/${tag}_tile_walk.ncu-rep --page details --csv > $o/${tag}_tile_kernel_walk_ncu_details.csv 2>/dev/null
 tail -3 $o/${tag}_pytest.log; tail -2 $o/${tag}_pytest_noalloc_alone.log; cut -c1-600 $o/${tag}_bench.json
