@@ -45,7 +45,8 @@ struct TileLaunch {
 };
 int band_count(int sublen, int excl);                    // total number of bands of the problem
 long long build_item_table(int sublen, int excl, int rank, int world, int seg_rows, std::vector<int> &item_start);
-int default_seg_rows(int sublen, int excl, int m, int world, int sm_count);
+// base_rows: the segment length aimed at when the problem has items to spare (shorter for small problems, never below 16 m)
+int default_seg_rows(int sublen, int excl, int m, int world, int sm_count, int base_rows);
 cudaError_t launch_tiles_f64(const double *df_dg, const double *nm, const double *mnc, const double *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 cudaError_t launch_tiles_f32(const float *df_dg, const float *nm, const float *mnc, const float *qt0, ProfileEntry *prof, const TileLaunch &p, cudaStream_t s);
 

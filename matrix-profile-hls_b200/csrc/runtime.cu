@@ -22,6 +22,16 @@
 #ifndef MPB_CHAIN_MARGIN_LOG2
 #define MPB_CHAIN_MARGIN_LOG2 0                  // near-tie margin of the chain-carry mode = 2^-k; 0 = by series length (default_margin_log2)
 #endif
+// Rows per re-seeded segment when the problem is large enough.  The re-seed costs m FMAs per diagonal and segment (6 % of a step at
+// 4224 rows, m = 256).  fp32 and the plain re-seeding modes rely on it to bound the chain's drift (fp32: 4.6e-5 at 4224 rows, n = 2^20,
+// against a 1e-4 budget), so they keep the shorter length; the chain-carry mode reproduces the reference's unbroken chain whatever
+// the cut, so it takes the longer one (-3 % on both series).
+#ifndef MPB_SEG_BASE
+#define MPB_SEG_BASE 4096
+#endif
+#ifndef MPB_SEG_BASE_CARRY
+#define MPB_SEG_BASE_CARRY 8192
+#endif
 #ifndef MPB_CHAIN_CHUNK_ITEMS
 #define MPB_CHAIN_CHUNK_ITEMS (1 << 19)          // work items per launch chunk of the chain-carry mode (4 KB of S_k + 4 KB of E_k each)
 #endif
@@ -87,11 +97,12 @@ int mpb_context_create(int ordinal, mpb_context **out) {
     if (!c) return fail(MPB_E_NOMEM, "out of host memory");
     c->device = ordinal;
     c->sm_count = prop.multiProcessorCount;
-    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU(cudaEventCreate(&c->mark));
-    CU(cudaEventCreate(&c->now));
-    CU(cudaEventRecord(c->mark, c->stream));
-    reg_add(g_ctxs, c);
+    reg_add(g_ctxs, c);               // from here on mpb_context_destroy(c) releases whatever was created
+    cudaError_t ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&c->mark);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&c->now);
+    if (ce == cudaSuccess) ce = cudaEventRecord(c->mark, c->stream);
+    if (ce != cudaSuccess) { mpb_context_destroy(c); return fail(MPB_E_CUDA, "creating the context's stream / events: %s", cudaGetErrorString(ce)); }
     *out = c;
     return MPB_OK;
 }
@@ -251,6 +262,7 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     if (dtype != MPB_F64 && dtype != MPB_F32) return fail(MPB_E_INVALID, "dtype must be MPB_F64 or MPB_F32");
     if (m < 4 || n < m) return fail(MPB_E_INVALID, "need n >= m >= 4 (n=%d, m=%d)", n, m);
     if (n - m + 1 <= m / 4) return fail(MPB_E_INVALID, "n-m+1 = %d does not exceed the exclusion zone m/4 = %d: no valid pair", n - m + 1, m / 4);
+    if (m > 14336) return fail(MPB_E_INVALID, "m = %d exceeds 14336: the precompute kernels stage 2 m doubles per CTA in shared memory (227 KB)", m);
     CU(cudaSetDevice(c->device));
     mpb_plan *p = new (std::nothrow) mpb_plan();
     if (!p) return fail(MPB_E_NOMEM, "out of host memory");
@@ -295,12 +307,13 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     }
 #undef ALLOC
     // zero padding beyond sublen is what lets tiles run off the matrix edge without bounds checks
-    CU(cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream));
-    CU(cudaMemsetAsync(p->inv, 0, es * np, c->stream));
-    CU(cudaMemsetAsync(p->qt0, 0, es * np, c->stream));
-    CU(cudaMemsetAsync(p->slow_counter, 0, 40 * sizeof(unsigned long long), c->stream));
-    if (p->chain_fix) CU(cudaMemsetAsync(p->chain_stats, 0, 4 * sizeof(unsigned long long), c->stream));
-    for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
+    cudaError_t ie = cudaMemsetAsync(p->df_dg, 0, 2 * es * np, c->stream);
+    if (ie == cudaSuccess) ie = cudaMemsetAsync(p->inv, 0, es * np, c->stream);
+    if (ie == cudaSuccess) ie = cudaMemsetAsync(p->qt0, 0, es * np, c->stream);
+    if (ie == cudaSuccess) ie = cudaMemsetAsync(p->slow_counter, 0, 40 * sizeof(unsigned long long), c->stream);
+    if (ie == cudaSuccess && p->chain_fix) ie = cudaMemsetAsync(p->chain_stats, 0, 4 * sizeof(unsigned long long), c->stream);
+    for (cudaEvent_t &e : p->ev) if (ie == cudaSuccess) ie = cudaEventCreate(&e);
+    if (ie != cudaSuccess) { mpb_plan_destroy(p); return fail(MPB_E_CUDA, "initialising the plan's buffers / events: %s", cudaGetErrorString(ie)); }
     p->tm.cells = mpb_useful_cells(n, m);
     *out = p;
     return MPB_OK;
@@ -332,7 +345,7 @@ int mpb_plan_set_sketch_bands(mpb_plan *p, int bands) {
 static int plan_build_table(mpb_plan *p) {
     if (!p->table_dirty) return MPB_OK;
     int seg = 0;
-    if (!(p->flags & MPB_FLAG_NO_RESEED)) seg = p->seg_rows >= 0 ? p->seg_rows : mpb::default_seg_rows(p->sublen, p->excl, p->m, 8 /* nominal rank count: keeps results independent of the GPU count */, p->ctx->sm_count);
+    if (!(p->flags & MPB_FLAG_NO_RESEED)) seg = p->seg_rows >= 0 ? p->seg_rows : mpb::default_seg_rows(p->sublen, p->excl, p->m, 8 /* nominal rank count: keeps results independent of the GPU count */, p->ctx->sm_count, p->chain_fix ? MPB_SEG_BASE_CARRY : MPB_SEG_BASE);
     std::vector<int> tab;
     const long long items = mpb::build_item_table(p->sublen, p->excl, p->rank, p->world, seg, tab);
     if (items > 0x7fffffffLL) return fail(MPB_E_INVALID, "%lld work items exceed the grid limit; raise the segment length", items);
