@@ -277,6 +277,9 @@ int mpb_plan_create(mpb_context *c, int n, int m, int dtype, unsigned flags, mpb
     // n = 2^16 / 2^18 / 2^20 / 2^22) and the margin must be 128 x the bound (chain_check); a wide margin only costs log
     // entries on very smooth series (m in the thousands), so it is not simply set to the largest value.
     p->margin_log2 = MPB_CHAIN_MARGIN_LOG2 ? MPB_CHAIN_MARGIN_LOG2 : (n <= (1 << 20) ? 17 : n <= (1 << 22) ? 15 : n <= (1 << 24) ? 13 : 11);
+    // short windows: a nearly flat window has a tiny norm, and the bound pairs the largest inverse norms of whole row / column blocks
+    // (measured bound at m = 32, n = 2^22, random walk: 2.4e-6, which needs 2^-11)
+    if (!MPB_CHAIN_MARGIN_LOG2) p->margin_log2 = std::max(9, p->margin_log2 - (m < 64 ? 4 : m < 128 ? 2 : 0));
     p->sublen = n - m + 1; p->excl = m / 4; p->np = mpb::padded_len(p->sublen);
     const size_t es = dtype == MPB_F64 ? 8 : 4, np = (size_t)p->np;
 #define ALLOC(ptr, bytes)                                                                            \
