@@ -198,6 +198,11 @@ def run_gpu_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    # stdout carries the JSON line(s) and nothing else: native libraries write there too (NCCL prints its version banner to stdout
+    # when NCCL_DEBUG is set), so file descriptor 1 is pointed at stderr for the run and the JSON goes to the original
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -222,7 +227,7 @@ def run_gpu_arm(args):
         args.m = m
         out = bench_config(args, mp, torch, dist, ctx, stream, flush, comm, fma_peak, peaks, rank, world, local, dtype)
         if rank == 0:
-            print(json.dumps(out), flush=True)
+            os.write(json_fd, (json.dumps(out) + "\n").encode())
     if comm is not None:
         comm.close()
     if world > 1:

@@ -9,6 +9,7 @@ nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > $o/${tag}_g
 ( time timeout 1500 python -m pytest tests -m gpu -x -q ) > $o/${tag}_pytest.log 2>&1
 echo "pytest rc=$?" >> $o/${tag}_pytest.log
 timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > $o/${tag}_pytest_noalloc_alone.log 2>&1
+timeout 300 python __graft_entry__.py smoke > $o/${tag}_smoke.log 2>&1
 timeout 600 python bench.py --steps 5 --warmup 3 > $o/${tag}_bench.json 2> $o/${tag}_bench.err
 timeout 300 python bench.py --impl reference --steps 1 --warmup 1 > $o/${tag}_bench_reference_arm.json 2>> $o/${tag}_bench.err
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches_walk.csv \
