@@ -34,7 +34,7 @@ sys.path.insert(0, os.path.join(ROOT, "matrix-profile-hls_b200", "python"))
 METRIC = "matrix-profile cell updates/sec"
 UNIT = "cells/s"
 REF_W = 4096              # MP_SIZE_W of the reference's README configuration (README.md:35)
-REF_NOMINAL_RATE = 1.6e8  # useful cells/s of one host thread running the reference's Vanilla kernel: sizes the sample
+REF_NOMINAL_RATE = 4.5e8  # useful cells/s of one host thread of the GPU boxes running the reference's Vanilla kernel (-O3 -march=native; measured 4.6-4.8e8 in round 2): sizes the sample
 
 
 def synth_series(n, kind, seed=1234):
@@ -116,7 +116,7 @@ def reference_sample_chunks(n, m, threads, target_s):
     return w, nit, list(range(it0, min(nit, it0 + threads)))
 
 
-def cpu_reference_sample(n, m, kind, target_s=12.0, threads=None):
+def cpu_reference_sample(n, m, kind, target_s=8.0, threads=None):
     """Times the reference's Vanilla kernel (kernel/MatrixProfileKernelVanilla.cpp, compiled unmodified into
     oracle/_ref/libmpref_fast.so with -O3 -march=native; the C restatement when the reference was not compiled here) on one
     diagonal chunk per host thread.  Returns the cpu_baseline object."""
@@ -396,7 +396,7 @@ def main():
     ap.add_argument("--m", type=int, default=256)
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
     ap.add_argument("--data", default="walk", choices=["uniform", "walk", "periodic"])
-    ap.add_argument("--ref-seconds", type=float, default=12.0, help="CPU seconds per reference sample")
+    ap.add_argument("--ref-seconds", type=float, default=8.0, help="CPU seconds per reference sample (one diagonal chunk per host thread; the same sample in the cpu_baseline leg and the --impl reference arm)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-second-series", action="store_true", help="skip the second series block (long configs)")
     ap.add_argument("--m-list", default="", help="comma list of subsequence lengths: one JSON line per m (BASELINE.json config 5)")
