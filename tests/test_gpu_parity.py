@@ -554,3 +554,29 @@ def test_tlf_chunks_at_w4096_n65536(mp, oracle):
     pick = rv > cv
     assert np.array_equal(np.where(pick, rv, cv), g["vanilla_corr"])
     assert np.array_equal(np.where(pick, ri, ci), g["vanilla_MPI"])
+
+
+def test_slots_without_a_positive_correlation(mp, ctx, oracle):
+    """Documented divergence: a slot whose valid correlations are all <= 0.  The reference's P = 0
+    substitution for excluded / out-of-range cells (Vanilla.cpp:72-84) then wins the max, so its value is 0 (distance
+    sqrt(2m)) and its index names an excluded column; the engine never walks excluded cells: same value, index -1."""
+    T, m = np.random.default_rng(3).standard_normal(24), 16
+    eMP, eMPI, ecorr, _ = oracle.run(T, m, 8)
+    zero = ecorr <= 0
+    assert zero.any() and not zero.all()
+    for flags in (0, mp.FLAG_STRICT):
+        plan = run_plan(mp, ctx, T, m, mp.F64, flags)
+        plan.finalize()
+        MP, MPI, corr = plan.download()
+        plan.close()
+        assert np.array_equal(corr[zero], ecorr[zero]) and np.array_equal(MP[zero], eMP[zero]), flags
+        assert (MPI[zero] == -1).all(), flags
+        assert np.abs(corr[~zero] - ecorr[~zero]).max() <= 1e-9 and np.array_equal(MPI[~zero], eMPI[~zero]), flags
+
+
+def test_window_longer_than_the_precompute_staging_is_rejected(mp, ctx):
+    """m beyond what the precompute kernels can stage in shared memory fails with MPB_E_INVALID and a message, not with an
+    opaque launch error."""
+    with pytest.raises(mp.MpbError) as e:
+        mp.Plan(ctx, 60000, 15000)
+    assert e.value.code == -1 and "14336" in str(e.value)
