@@ -25,7 +25,7 @@ for k, (a, op, t) in enumerate(ins):
         if mm and int(mm.group(1), 16) <= a:
             tgt = int(mm.group(1), 16)
             k0 = next(i for i, x in enumerate(ins) if x[0] == tgt)
-            fma = sum(1 for x in ins[k0:k + 1] if x[1].startswith(("DFMA", "FFMA")))
+            fma = sum((2 if x[1].startswith("FFMA2") else 1) for x in ins[k0:k + 1] if x[1].startswith(("DFMA", "FFMA")))
             loops.append((fma, k0, k))
 fma, k0, k1 = max(loops)
 seg = ins[k0:k1 + 1]
