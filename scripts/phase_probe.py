@@ -24,9 +24,9 @@ nlb = min(p.local_bands() for p in plans)
 
 
 def breakpoints(s):
-    if s == "auto":                       # the schedule dist.compute_merged uses
+    if s == "auto":                       # the schedule mpb_plan_compute_merged uses without peer access (a function of the JOB's band count)
         from mpb200.dist import merge_points
-        return merge_points(nlb, W) + [-1]
+        return merge_points(sum(p.local_bands() for p in plans), W) + [-1]
     if s.startswith("geo:"):
         _, first, ratio = s.split(":"); b, out = float(first), []
         while b < nlb: out.append(int(round(b))); b *= float(ratio)

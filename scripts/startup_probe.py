@@ -15,7 +15,7 @@ cuts = [0, 1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64]
 for world, rank in ((1, 0), (8, 3)):
     for sk in (0, 1):
         p = mp.Plan(ctx, n, 256, mp.F64, 0); p.set_shard(rank, world); p.set_sketch_bands(sk)
-            p.upload_series(T)
+        p.upload_series(T)
         for rep in range(2):
             p.precompute(); ctx.finish()
             ms = []
