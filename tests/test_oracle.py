@@ -118,6 +118,23 @@ def test_oracle_vs_ref_shim_random_shapes(oracle):
 
 
 @needs_ref
+def test_p_zero_clamp_names_an_excluded_column(oracle):
+    """The edge the GPU engine documents a divergence for (DESIGN.md section 2, tests/test_gpu_parity.py::
+    test_slots_without_a_positive_correlation): when every valid correlation of a slot is negative, the reference's P = 0 substitution
+    for excluded / out-of-range cells (Vanilla.cpp:72-84) wins -- value 0, index of a column INSIDE the exclusion zone.  Pinned here on
+    the reference's own kernel and on the restatement."""
+    T, m = np.random.default_rng(3).standard_normal(24), 16
+    for w in (8, 32):
+        MP, MPI, corr, _ = RefShim().run(T, m, w)
+        oMP, oMPI, ocorr, _ = oracle.run(T, m, w)
+        assert np.array_equal(corr, ocorr) and np.array_equal(MPI, oMPI) and np.array_equal(MP, oMP)
+        zero = np.nonzero(corr == 0)[0]
+        assert zero.size >= 1 and (corr >= 0).all()
+        assert all(abs(int(MPI[i]) - int(i)) < m // 4 for i in zero)          # the "neighbour" is an excluded column
+        assert np.array_equal(MP[zero], np.full(zero.size, np.sqrt(2.0 * m)))
+
+
+@needs_ref
 @pytest.mark.parametrize("exe", ["testVanillaKernel", "testTiledKernel"])
 def test_reference_own_gtest_suites_pass(exe):
     """The reference's eight known-answer tests, unmodified, compiled by oracle/Makefile."""
